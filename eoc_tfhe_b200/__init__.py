@@ -1,0 +1,13 @@
+"""eoc_tfhe_b200 -- B200-native TFHE gate bootstrapping behind libtfhe's gate API.
+
+Host-side mirror (Python) of the C ABI in include/b200tfhe.h.  The compute path is the CUDA
+library eoc_tfhe_b200/libb200tfhe.so; importing this package never falls back to a CPU
+implementation -- `lib.load()` raises if the library is missing.
+
+(The directory is spelled with an underscore because `eoc-tfhe_b200` is not importable.)
+"""
+from .lib import load, LIB_PATH, B200Error  # noqa: F401
+from .engine import (  # noqa: F401
+    GateOp, Params, CloudKey, PARAMS_80, PARAMS_128,
+)
+from . import circuits, wire  # noqa: F401

@@ -1,0 +1,613 @@
+// abi.cpp -- host side of libb200tfhe.so: the C ABI declared in include/b200tfhe.h.
+//
+// Mirrors the reference's operator interface for the gate-bootstrapping path
+// (libs/tfhe/src/include/tfhe_gate_bootstrapping_functions.h:14-87, include/tfhe.h:42-45,
+// include/lwe-functions.h:79): same names, argument meaning, aliasing and error behaviour.
+// No CPU implementation of the path exists in this library: every entry needs a CUDA device.
+#include "../../include/b200tfhe.h"
+#include "engine.cuh"
+#include "host_state.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+using namespace b200;
+
+// ------------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string t_last_error;
+int b200_fail(const std::string &msg) {
+    t_last_error = msg;
+    return 1;
+}
+int b200_fail_cuda(const char *what, cudaError_t e) {
+    return b200_fail(std::string(what) + ": " + cudaGetErrorString(e));
+}
+static int fail(const std::string &msg) { return b200_fail(msg); }
+static int fail_cuda(const char *what, cudaError_t e) { return b200_fail_cuda(what, e); }
+#define CK(call) B200_CK(call)
+
+extern "C" const char *b200_last_error(void) { return t_last_error.c_str(); }
+
+static void die(const char *fn) {
+    // the reference's void gates abort on fatal errors (tfhe_gate_bootstrapping.cpp:11-15)
+    std::fprintf(stderr, "libb200tfhe: %s failed: %s\n", fn, t_last_error.c_str());
+    std::abort();
+}
+
+// ------------------------------------------------------------------------------------------------
+// key object
+// ------------------------------------------------------------------------------------------------
+static int g_device = 0;
+static std::mutex g_cache_mu;
+static std::map<const void *, b200_key *> g_by_cloud, g_by_bkfft, g_by_ks;
+
+extern "C" int b200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+extern "C" int b200_set_device(int device) {
+    CK(cudaSetDevice(device));
+    g_device = device;
+    return 0;
+}
+extern "C" int64_t b200_launch_count(void) { return launch_count(); }
+
+static int check_params(const b200_params *p) {
+    if (!p) return fail("params is NULL");
+    if (p->N != 1024) return fail("only N=1024 is supported (as in every reference FFT processor)");
+    if (p->k != 1) return fail("only k=1 is supported");
+    if (p->n < 1 || p->n > 639) return fail("n out of range (1..639)");
+    const bool ok = (p->l == 2 && p->Bgbit == 10) || (p->l == 3 && p->Bgbit == 7) || (p->l == 2 && p->Bgbit == 8) ||
+                    (p->l == 1 && p->Bgbit == 16) || (p->l == 4 && p->Bgbit == 6);
+    if (!ok) return fail("unsupported (l, Bgbit); built: (2,10) (3,7) (2,8) (1,16) (4,6)");
+    if (p->ks_t != 8 || p->ks_basebit != 2) return fail("only ks_t=8, ks_basebit=2 is supported (both reference sets)");
+    return 0;
+}
+
+static int key_alloc(const b200_params *p, b200_key **out) {
+    if (!out) return fail("out is NULL");
+    *out = nullptr;
+    if (check_params(p)) return 1;
+    if (b200_device_count() <= 0) return fail("no CUDA device: libb200tfhe has no CPU fallback");
+    CK(cudaSetDevice(g_device));
+    b200_key *k = new b200_key();
+    DeviceKey &d = k->dk;
+    d.n = p->n; d.N = p->N; d.k = p->k; d.l = p->l; d.Bgbit = p->Bgbit;
+    d.ks_t = p->ks_t; d.ks_basebit = p->ks_basebit; d.ks_variance = p->ks_variance;
+    d.ks_stride = (p->n + 1 + 3) & ~3;
+    d.device = g_device;
+    const int kpl = (d.k + 1) * d.l, base = 1 << d.ks_basebit;
+    d.bkfft_bytes = (size_t)d.n * kpl * (d.k + 1) * (d.N / 2) * sizeof(double2);
+    d.ks_bytes = (size_t)d.N * d.k * d.ks_t * (base - 1) * d.ks_stride * sizeof(int32_t);
+    cudaError_t e = cudaMalloc((void **)&d.bkfft, d.bkfft_bytes);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&d.ks, d.ks_bytes);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking);
+    for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&k->ev[i]);
+    if (e == cudaSuccess) e = upload_twiddles();
+    if (e != cudaSuccess) {
+        fail_cuda("key allocation", e);
+        b200_key_free(k);
+        return 1;
+    }
+    *out = k;
+    return 0;
+}
+
+extern "C" int b200_key_create_empty(const b200_params *p, b200_key **out) {
+    if (key_alloc(p, out)) return 1;
+    (*out)->filled = true;  // caller fills the blobs (broadcast) before use
+    return 0;
+}
+
+extern "C" int b200_key_create(const b200_params *p, const int32_t *bk_coefs, const int32_t *ks_rows, b200_key **out) {
+    if (!bk_coefs || !ks_rows) return fail("bk_coefs / ks_rows is NULL");
+    if (key_alloc(p, out)) return 1;
+    b200_key *k = *out;
+    const DeviceKey &d = k->dk;
+    const int kpl = (d.k + 1) * d.l, base = 1 << d.ks_basebit;
+    const size_t bk_ints = (size_t)d.n * kpl * (d.k + 1) * d.N;
+    const size_t ks_ints = (size_t)d.N * d.k * d.ks_t * base * (d.n + 1);
+    DevBuf tmp;
+    int rc = 0;
+    do {
+        if ((rc = tmp.ensure(std::max(bk_ints, ks_ints) * sizeof(int32_t)))) break;
+        cudaError_t e = cudaMemcpyAsync(tmp.p, bk_coefs, bk_ints * sizeof(int32_t), cudaMemcpyHostToDevice, k->stream);
+        if (e == cudaSuccess) e = launch_bk_convert(d, (const int32_t *)tmp.p, k->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(k->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(tmp.p, ks_rows, ks_ints * sizeof(int32_t), cudaMemcpyHostToDevice, k->stream);
+        if (e == cudaSuccess) e = launch_ks_pack(d, (const int32_t *)tmp.p, k->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(k->stream);
+        if (e != cudaSuccess) rc = fail_cuda("key upload/convert", e);
+    } while (0);
+    tmp.release();
+    if (rc) {
+        b200_key_free(k);
+        *out = nullptr;
+        return 1;
+    }
+    k->filled = true;
+    return 0;
+}
+
+extern "C" void b200_key_free(b200_key *k) {
+    if (!k) return;
+    {
+        std::lock_guard<std::mutex> g(g_cache_mu);
+        for (auto *m : {&g_by_cloud, &g_by_bkfft, &g_by_ks})
+            for (auto it = m->begin(); it != m->end();) it = (it->second == k) ? m->erase(it) : std::next(it);
+    }
+    cudaSetDevice(k->dk.device);
+    if (k->stream) cudaStreamSynchronize(k->stream);
+    if (k->dk.bkfft) cudaFree(k->dk.bkfft);
+    if (k->dk.ks) cudaFree(k->dk.ks);
+    for (DevBuf *b : {&k->u, &k->in0, &k->in1, &k->in2, &k->out, &k->nz, &k->desc_rot, &k->desc_ks, &k->desc_lin, &k->acc}) b->release();
+    k->stage_in.release();
+    k->stage_out.release();
+    for (auto &e : k->ev)
+        if (e) cudaEventDestroy(e);
+    if (k->stream) cudaStreamDestroy(k->stream);
+    delete k;
+}
+
+extern "C" int b200_key_params(const b200_key *k, b200_params *out) {
+    if (!k || !out) return fail("NULL argument");
+    out->n = k->dk.n; out->N = k->dk.N; out->k = k->dk.k; out->l = k->dk.l; out->Bgbit = k->dk.Bgbit;
+    out->ks_t = k->dk.ks_t; out->ks_basebit = k->dk.ks_basebit; out->ks_variance = k->dk.ks_variance;
+    return 0;
+}
+
+extern "C" int b200_key_device_blobs(const b200_key *k, void **d_bkfft, size_t *bkfft_bytes, void **d_ks, size_t *ks_bytes) {
+    if (!k) return fail("key is NULL");
+    if (d_bkfft) *d_bkfft = k->dk.bkfft;
+    if (bkfft_bytes) *bkfft_bytes = k->dk.bkfft_bytes;
+    if (d_ks) *d_ks = k->dk.ks;
+    if (ks_bytes) *ks_bytes = k->dk.ks_bytes;
+    return 0;
+}
+
+// ---- from a live libtfhe cloud key ---------------------------------------------------------------
+extern "C" int b200_cloudkey_upload(const TFheGateBootstrappingCloudKeySet *ck, b200_key **out) {
+    if (!ck || !ck->params || !ck->bk) return fail("cloud key (or its params / bk) is NULL");
+    {
+        std::lock_guard<std::mutex> g(g_cache_mu);
+        auto it = g_by_cloud.find(ck);
+        if (it != g_by_cloud.end()) {
+            if (out) *out = it->second;
+            return 0;
+        }
+    }
+    const TFheGateBootstrappingParameterSet *ps = ck->params;
+    const TGswParams *gp = ps->tgsw_params;
+    const TLweParams *tp = gp->tlwe_params;
+    const LweKeySwitchKey *ks = (ck->bkFFT && ck->bkFFT->ks) ? ck->bkFFT->ks : ck->bk->ks;
+    if (!ks) return fail("cloud key has no key-switch key");
+    b200_params p;
+    p.n = ps->in_out_params->n; p.N = tp->N; p.k = tp->k; p.l = gp->l; p.Bgbit = gp->Bgbit;
+    p.ks_t = ps->ks_t; p.ks_basebit = ps->ks_basebit;
+    if (check_params(&p)) return 1;
+    if (ks->n != p.N * p.k || ks->t != p.ks_t || ks->basebit != p.ks_basebit) return fail("key-switch key shape mismatch");
+    const int kpl = (p.k + 1) * p.l, base = 1 << p.ks_basebit, n1 = p.n + 1;
+    p.ks_variance = ks->ks[0][0][1].current_variance;
+    std::vector<int32_t> bk((size_t)p.n * kpl * (p.k + 1) * p.N), rows((size_t)ks->n * p.ks_t * base * n1);
+    for (int i = 0; i < p.n; ++i)
+        for (int r = 0; r < kpl; ++r)
+            for (int c = 0; c <= p.k; ++c)
+                std::memcpy(&bk[(((size_t)i * kpl + r) * (p.k + 1) + c) * p.N], ck->bk->bk[i].all_sample[r].a[c].coefsT,
+                            p.N * sizeof(int32_t));
+    for (int i = 0; i < ks->n; ++i)
+        for (int j = 0; j < p.ks_t; ++j)
+            for (int h = 0; h < base; ++h) {
+                int32_t *dst = &rows[(((size_t)i * p.ks_t + j) * base + h) * n1];
+                const LweSample &s = ks->ks[i][j][h];
+                std::memcpy(dst, s.a, p.n * sizeof(int32_t));
+                dst[p.n] = s.b;
+            }
+    b200_key *k = nullptr;
+    if (b200_key_create(&p, bk.data(), rows.data(), &k)) return 1;
+    {
+        std::lock_guard<std::mutex> g(g_cache_mu);
+        g_by_cloud[ck] = k;
+        if (ck->bkFFT) g_by_bkfft[ck->bkFFT] = k;
+        g_by_ks[ks] = k;
+        if (ck->bk->ks) g_by_ks[ck->bk->ks] = k;
+    }
+    if (out) *out = k;
+    return 0;
+}
+
+extern "C" void b200_cloudkey_forget(const TFheGateBootstrappingCloudKeySet *ck) {
+    b200_key *k = nullptr;
+    {
+        std::lock_guard<std::mutex> g(g_cache_mu);
+        auto it = g_by_cloud.find(ck);
+        if (it == g_by_cloud.end()) return;
+        k = it->second;
+    }
+    b200_key_free(k);
+}
+
+// ------------------------------------------------------------------------------------------------
+// gate batches
+// ------------------------------------------------------------------------------------------------
+static bool op_is_linear(int op) { return op == B200_NOT || op == B200_COPY || op == B200_CONST0 || op == B200_CONST1; }
+static bool op_valid(int op) { return op >= 0 && op < B200_GATE_OP_COUNT; }
+static constexpr int64_t kChunkItems = 1 << 18;  // rotations per launch: bounds the extracted-sample workspace to ~1 GiB
+
+// enqueue: out[count] = op(a, b, c) on device pointers. Caller holds key->mu.
+static int enqueue_gates(b200_key *k, int op, int32_t *d_out, const int32_t *d_a, const int32_t *d_b, const int32_t *d_c,
+                         int64_t count, int32_t *d_nonzero, cudaStream_t s, bool timed) {
+    const DeviceKey &d = k->dk;
+    const int n1 = d.n + 1;
+    if (op_is_linear(op)) {
+        const int sign = op == B200_NOT ? -1 : 1;
+        const int32_t cst = op == B200_CONST1 ? (1 << 29) : (op == B200_CONST0 ? -(1 << 29) : 0);
+        const int32_t *in = (op == B200_NOT || op == B200_COPY) ? d_a : nullptr;
+        if ((op == B200_NOT || op == B200_COPY) && !d_a) return fail("input a is NULL");
+        CK(launch_linear(d, d_out, in, sign, cst, count, s));
+        return 0;
+    }
+    if (!d_a || !d_b || (op == B200_MUX && !d_c)) return fail("gate input pointer is NULL");
+    const int per = op == B200_MUX ? 2 : 1;
+    const int64_t chunk_gates = kChunkItems / per;
+    if (k->u.ensure((size_t)std::min<int64_t>(count, chunk_gates) * per * (d.N + 1) * sizeof(int32_t))) return 1;
+    for (int64_t g0 = 0; g0 < count; g0 += chunk_gates) {
+        const int64_t g = std::min(chunk_gates, count - g0);
+        BlindRotateArgs br{};
+        br.in0 = d_a + g0 * n1;
+        br.in1 = d_b + g0 * n1;
+        br.in2 = d_c ? d_c + g0 * n1 : nullptr;
+        br.op = op;
+        br.mu = 1 << 29;
+        br.u = (int32_t *)k->u.p;
+        br.items = g * per;
+        const bool t = timed && g0 == 0;
+        if (t) CK(cudaEventRecord(k->ev[0], s));
+        CK(launch_blind_rotate(d, br, s));
+        if (t) CK(cudaEventRecord(k->ev[1], s));
+        KeySwitchArgs ks{};
+        ks.u = (const int32_t *)k->u.p;
+        ks.pair = per == 2;
+        ks.out = d_out + g0 * n1;
+        ks.nonzero = d_nonzero ? d_nonzero + g0 : nullptr;
+        ks.items = g;
+        CK(launch_keyswitch(d, ks, s));
+        if (t) CK(cudaEventRecord(k->ev[2], s));
+    }
+    return 0;
+}
+
+extern "C" int b200_gate_batch_dev(b200_key *k, int op, int32_t *d_out, const int32_t *d_a, const int32_t *d_b,
+                                   const int32_t *d_c, int64_t count, void *stream) {
+    if (!k || !k->filled) return fail("key is NULL or not filled");
+    if (!op_valid(op)) return fail("invalid gate op");
+    if (count < 0) return fail("negative count");
+    if (count == 0) return 0;
+    if (!d_out) return fail("d_out is NULL");
+    std::lock_guard<std::mutex> g(k->mu);
+    CK(cudaSetDevice(k->dk.device));
+    k->timing_pending = true;
+    return enqueue_gates(k, op, d_out, d_a, d_b, d_c, count, nullptr, (cudaStream_t)stream, true);
+}
+
+static int gate_batch_host_locked(b200_key *k, int op, int32_t *out, const int32_t *a, const int32_t *b, const int32_t *c,
+                                  int64_t count, int32_t *nonzero) {
+    const DeviceKey &d = k->dk;
+    const size_t bytes = (size_t)count * (d.n + 1) * sizeof(int32_t);
+    cudaStream_t s = k->stream;
+    CK(cudaSetDevice(d.device));
+    const bool need_a = !(op == B200_CONST0 || op == B200_CONST1);
+    const bool need_b = !op_is_linear(op);
+    const bool need_c = op == B200_MUX;
+    if ((need_a && !a) || (need_b && !b) || (need_c && !c) || !out) return fail("NULL batch pointer");
+    CK(cudaEventRecord(k->ev[3], s));
+    if (need_a) { if (k->in0.ensure(bytes)) return 1; CK(cudaMemcpyAsync(k->in0.p, a, bytes, cudaMemcpyHostToDevice, s)); }
+    if (need_b) { if (k->in1.ensure(bytes)) return 1; CK(cudaMemcpyAsync(k->in1.p, b, bytes, cudaMemcpyHostToDevice, s)); }
+    if (need_c) { if (k->in2.ensure(bytes)) return 1; CK(cudaMemcpyAsync(k->in2.p, c, bytes, cudaMemcpyHostToDevice, s)); }
+    if (k->out.ensure(bytes)) return 1;
+    int32_t *d_nz = nullptr;
+    if (nonzero && !op_is_linear(op)) {
+        if (k->nz.ensure((size_t)count * sizeof(int32_t))) return 1;
+        d_nz = (int32_t *)k->nz.p;
+        CK(cudaMemsetAsync(d_nz, 0, (size_t)count * sizeof(int32_t), s));
+    }
+    if (enqueue_gates(k, op, (int32_t *)k->out.p, (const int32_t *)k->in0.p, (const int32_t *)k->in1.p,
+                      (const int32_t *)k->in2.p, count, d_nz, s, true))
+        return 1;
+    CK(cudaMemcpyAsync(out, k->out.p, bytes, cudaMemcpyDeviceToHost, s));
+    if (d_nz) CK(cudaMemcpyAsync(nonzero, d_nz, (size_t)count * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    else if (nonzero) std::memset(nonzero, 0, (size_t)count * sizeof(int32_t));
+    CK(cudaStreamSynchronize(s));
+    k->timing_pending = !op_is_linear(op);
+    return 0;
+}
+
+extern "C" int b200_gate_batch_host(b200_key *k, int op, int32_t *out, const int32_t *a, const int32_t *b,
+                                    const int32_t *c, int64_t count) {
+    if (!k || !k->filled) return fail("key is NULL or not filled");
+    if (!op_valid(op)) return fail("invalid gate op");
+    if (count < 0) return fail("negative count");
+    if (count == 0) return 0;
+    std::lock_guard<std::mutex> g(k->mu);
+    return gate_batch_host_locked(k, op, out, a, b, c, count, nullptr);
+}
+
+extern "C" int b200_last_timing_ms(b200_key *k, float out_ms[3]) {
+    if (!k || !out_ms) return fail("NULL argument");
+    std::lock_guard<std::mutex> g(k->mu);
+    CK(cudaSetDevice(k->dk.device));
+    if (k->timing_pending) {
+        CK(cudaEventSynchronize(k->ev[2]));
+        CK(cudaEventElapsedTime(&k->last_ms[0], k->ev[0], k->ev[1]));
+        CK(cudaEventElapsedTime(&k->last_ms[1], k->ev[1], k->ev[2]));
+        float tot = 0;
+        if (cudaEventElapsedTime(&tot, k->ev[3], k->ev[2]) == cudaSuccess) k->last_ms[2] = tot;
+        else { cudaGetLastError(); k->last_ms[2] = k->last_ms[0] + k->last_ms[1]; }
+        k->timing_pending = false;
+    }
+    out_ms[0] = k->last_ms[0]; out_ms[1] = k->last_ms[1]; out_ms[2] = k->last_ms[2];
+    return 0;
+}
+
+// ---- batched gate over libtfhe samples -----------------------------------------------------------
+static int gate_batch_samples(b200_key *k, int op, LweSample *const *out, const LweSample *const *a,
+                              const LweSample *const *b, const LweSample *const *c, int32_t count) {
+    const int n = k->dk.n, n1 = n + 1;
+    const bool need_a = !(op == B200_CONST0 || op == B200_CONST1);
+    const bool need_b = !op_is_linear(op), need_c = op == B200_MUX;
+    if (!out || (need_a && !a) || (need_b && !b) || (need_c && !c)) return fail("NULL sample array");
+    std::lock_guard<std::mutex> g(k->mu);
+    const size_t row = (size_t)n1 * sizeof(int32_t), bytes = row * count;
+    if (k->stage_in.ensure(3 * bytes) || k->stage_out.ensure(bytes + (size_t)count * sizeof(int32_t))) return 1;
+    int32_t *ha = (int32_t *)k->stage_in.p, *hb = ha + (size_t)count * n1, *hc = hb + (size_t)count * n1;
+    int32_t *ho = (int32_t *)k->stage_out.p, *hnz = ho + (size_t)count * n1;
+    auto gather = [&](int32_t *dst, const LweSample *const *src) {
+        for (int32_t i = 0; i < count; ++i) {
+            std::memcpy(dst + (size_t)i * n1, src[i]->a, n * sizeof(int32_t));
+            dst[(size_t)i * n1 + n] = src[i]->b;
+        }
+    };
+    // snapshot semantics: all inputs are staged before any output is written
+    if (need_a) gather(ha, a);
+    if (need_b) gather(hb, b);
+    if (need_c) gather(hc, c);
+    if (gate_batch_host_locked(k, op, ho, ha, hb, hc, count, hnz)) return 1;
+    for (int32_t i = 0; i < count; ++i) {
+        std::memcpy(out[i]->a, ho + (size_t)i * n1, n * sizeof(int32_t));
+        out[i]->b = ho[(size_t)i * n1 + n];
+        if (op_is_linear(op)) {
+            // lweNegate / lweCopy keep the variance, lweNoiselessTrivial sets 0 (lwe-functions.cpp:120-135)
+            out[i]->current_variance = need_a ? a[i]->current_variance : 0.0;
+        } else {
+            out[i]->current_variance = hnz[i] * k->dk.ks_variance;
+        }
+    }
+    return 0;
+}
+
+static b200_key *key_for_cloud(const TFheGateBootstrappingCloudKeySet *ck) {
+    b200_key *k = nullptr;
+    if (b200_cloudkey_upload(ck, &k)) return nullptr;
+    return k;
+}
+
+extern "C" int bootsGate_batch(int op, LweSample *const *out, const LweSample *const *a, const LweSample *const *b,
+                               const LweSample *const *c, int32_t count, const TFheGateBootstrappingCloudKeySet *bk) {
+    if (!op_valid(op)) return fail("invalid gate op");
+    if (count < 0) return fail("negative count");
+    if (count == 0) return 0;
+    b200_key *k = key_for_cloud(bk);
+    if (!k) return 1;
+    return gate_batch_samples(k, op, out, a, b, c, count);
+}
+
+// ---- libtfhe drop-in gates (batch of one: the latency path) ----------------------------------------
+static void gate1(const char *name, int op, LweSample *r, const LweSample *a, const LweSample *b, const LweSample *c,
+                  const TFheGateBootstrappingCloudKeySet *bk) {
+    LweSample *outs[1] = {r};
+    const LweSample *as[1] = {a}, *bs[1] = {b}, *cs[1] = {c};
+    if (bootsGate_batch(op, outs, a ? as : nullptr, b ? bs : nullptr, c ? cs : nullptr, 1, bk)) die(name);
+}
+#define BINARY_GATE(NAME, OP)                                                                                     \
+    extern "C" void NAME(LweSample *r, const LweSample *a, const LweSample *b, const TFheGateBootstrappingCloudKeySet *bk) { \
+        gate1(#NAME, OP, r, a, b, nullptr, bk);                                                                   \
+    }
+BINARY_GATE(bootsNAND, B200_NAND)
+BINARY_GATE(bootsOR, B200_OR)
+BINARY_GATE(bootsAND, B200_AND)
+BINARY_GATE(bootsXOR, B200_XOR)
+BINARY_GATE(bootsXNOR, B200_XNOR)
+BINARY_GATE(bootsNOR, B200_NOR)
+BINARY_GATE(bootsANDNY, B200_ANDNY)
+BINARY_GATE(bootsANDYN, B200_ANDYN)
+BINARY_GATE(bootsORNY, B200_ORNY)
+BINARY_GATE(bootsORYN, B200_ORYN)
+extern "C" void bootsMUX(LweSample *r, const LweSample *a, const LweSample *b, const LweSample *c,
+                         const TFheGateBootstrappingCloudKeySet *bk) {
+    gate1("bootsMUX", B200_MUX, r, a, b, c, bk);
+}
+// The linear gates never touch the device in the reference either (boot-gates.cpp:164-189); they are
+// n+1 integer moves on caller memory, done in place here so that result may alias ca.
+extern "C" void bootsNOT(LweSample *r, const LweSample *a, const TFheGateBootstrappingCloudKeySet *bk) {
+    const int n = bk->params->in_out_params->n;
+    for (int i = 0; i < n; ++i) r->a[i] = -a->a[i];
+    r->b = -a->b;
+    r->current_variance = a->current_variance;
+}
+extern "C" void bootsCOPY(LweSample *r, const LweSample *a, const TFheGateBootstrappingCloudKeySet *bk) {
+    const int n = bk->params->in_out_params->n;
+    for (int i = 0; i < n; ++i) r->a[i] = a->a[i];
+    r->b = a->b;
+    r->current_variance = a->current_variance;
+}
+extern "C" void bootsCONSTANT(LweSample *r, int32_t value, const TFheGateBootstrappingCloudKeySet *bk) {
+    const int n = bk->params->in_out_params->n;
+    for (int i = 0; i < n; ++i) r->a[i] = 0;
+    r->b = value ? (1 << 29) : -(1 << 29);
+    r->current_variance = 0.0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// pieces of the path
+// ------------------------------------------------------------------------------------------------
+static int woks_locked(b200_key *k, int32_t *u, const int32_t *x, int32_t mu, int64_t count) {
+    const DeviceKey &d = k->dk;
+    cudaStream_t s = k->stream;
+    CK(cudaSetDevice(d.device));
+    const size_t in_bytes = (size_t)count * (d.n + 1) * 4, u_bytes = (size_t)count * (d.N + 1) * 4;
+    if (k->in0.ensure(in_bytes) || k->u.ensure(u_bytes)) return 1;
+    CK(cudaMemcpyAsync(k->in0.p, x, in_bytes, cudaMemcpyHostToDevice, s));
+    BlindRotateArgs br{};
+    br.in0 = (const int32_t *)k->in0.p;
+    br.op = kOpRaw;
+    br.mu = mu;
+    br.u = (int32_t *)k->u.p;
+    br.items = count;
+    CK(launch_blind_rotate(d, br, s));
+    CK(cudaMemcpyAsync(u, k->u.p, u_bytes, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return 0;
+}
+extern "C" int b200_bootstrap_woks_host(b200_key *k, int32_t *u, const int32_t *x, int32_t mu, int64_t count) {
+    if (!k || !k->filled) return fail("key is NULL or not filled");
+    if (count < 0 || count > kChunkItems) return fail("count out of range");
+    if (count == 0) return 0;
+    if (!u || !x) return fail("NULL batch pointer");
+    std::lock_guard<std::mutex> g(k->mu);
+    return woks_locked(k, u, x, mu, count);
+}
+
+extern "C" int b200_keyswitch_dev(b200_key *k, int32_t *d_out, const int32_t *d_u, int64_t count, void *stream) {
+    if (!k || !k->filled) return fail("key is NULL or not filled");
+    if (count < 0) return fail("negative count");
+    if (count == 0) return 0;
+    if (!d_out || !d_u) return fail("NULL device pointer");
+    std::lock_guard<std::mutex> g(k->mu);
+    CK(cudaSetDevice(k->dk.device));
+    KeySwitchArgs ks{};
+    ks.u = d_u;
+    ks.out = d_out;
+    ks.items = count;
+    CK(launch_keyswitch(k->dk, ks, (cudaStream_t)stream));
+    return 0;
+}
+
+static int keyswitch_locked(b200_key *k, int32_t *out, const int32_t *u, int32_t *nonzero, int64_t count) {
+    const DeviceKey &d = k->dk;
+    cudaStream_t s = k->stream;
+    CK(cudaSetDevice(d.device));
+    const size_t out_bytes = (size_t)count * (d.n + 1) * 4, u_bytes = (size_t)count * (d.N + 1) * 4;
+    if (k->u.ensure(u_bytes) || k->out.ensure(out_bytes) || k->nz.ensure((size_t)count * 4)) return 1;
+    CK(cudaMemcpyAsync(k->u.p, u, u_bytes, cudaMemcpyHostToDevice, s));
+    CK(cudaMemsetAsync(k->nz.p, 0, (size_t)count * 4, s));
+    KeySwitchArgs ks{};
+    ks.u = (const int32_t *)k->u.p;
+    ks.out = (int32_t *)k->out.p;
+    ks.nonzero = (int32_t *)k->nz.p;
+    ks.items = count;
+    CK(launch_keyswitch(d, ks, s));
+    CK(cudaMemcpyAsync(out, k->out.p, out_bytes, cudaMemcpyDeviceToHost, s));
+    if (nonzero) CK(cudaMemcpyAsync(nonzero, k->nz.p, (size_t)count * 4, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return 0;
+}
+extern "C" int b200_keyswitch_host(b200_key *k, int32_t *out, const int32_t *u, int32_t *nonzero, int64_t count) {
+    if (!k || !k->filled) return fail("key is NULL or not filled");
+    if (count < 0 || count > kChunkItems) return fail("count out of range");
+    if (count == 0) return 0;
+    if (!out || !u) return fail("NULL batch pointer");
+    std::lock_guard<std::mutex> g(k->mu);
+    return keyswitch_locked(k, out, u, nonzero, count);
+}
+
+static int cmux_host(b200_key *k, int32_t *acc, int32_t bk_index, int32_t barai, int mode, int64_t count) {
+    if (!k || !k->filled) return fail("key is NULL or not filled");
+    if (count < 0) return fail("negative count");
+    if (count == 0) return 0;
+    if (!acc) return fail("acc is NULL");
+    if (bk_index < 0 || bk_index >= k->dk.n) return fail("bk_index out of range");
+    if (barai < 0 || barai >= 2 * k->dk.N) return fail("barai out of range");
+    std::lock_guard<std::mutex> g(k->mu);
+    const DeviceKey &d = k->dk;
+    cudaStream_t s = k->stream;
+    CK(cudaSetDevice(d.device));
+    const size_t bytes = (size_t)count * (d.k + 1) * d.N * 4;
+    if (k->acc.ensure(bytes)) return 1;
+    CK(cudaMemcpyAsync(k->acc.p, acc, bytes, cudaMemcpyHostToDevice, s));
+    CK(launch_cmux_test(d, (int32_t *)k->acc.p, bk_index, barai, mode, count, s));
+    CK(cudaMemcpyAsync(acc, k->acc.p, bytes, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return 0;
+}
+extern "C" int b200_cmux_step_host(b200_key *k, int32_t *acc, int32_t bk_index, int32_t barai, int64_t count) {
+    return cmux_host(k, acc, bk_index, barai, 0, count);
+}
+extern "C" int b200_extern_product_host(b200_key *k, int32_t *acc, int32_t bk_index, int64_t count) {
+    return cmux_host(k, acc, bk_index, 0, 1, count);
+}
+
+// ---- lower-level libtfhe names ----------------------------------------------------------------------
+static b200_key *lookup(std::map<const void *, b200_key *> &m, const void *p) {
+    std::lock_guard<std::mutex> g(g_cache_mu);
+    auto it = m.find(p);
+    return it == m.end() ? nullptr : it->second;
+}
+extern "C" void tfhe_bootstrap_woKS_FFT(LweSample *result, const LweBootstrappingKeyFFT *bk, Torus32 mu, const LweSample *x) {
+    b200_key *k = lookup(g_by_bkfft, bk);
+    if (!k) { fail("bootstrapping key unknown: call b200_cloudkey_upload on its cloud key first"); die("tfhe_bootstrap_woKS_FFT"); }
+    const int n = k->dk.n, N = k->dk.N;
+    std::vector<int32_t> xin(n + 1), u(N + 1);
+    std::memcpy(xin.data(), x->a, n * 4);
+    xin[n] = x->b;
+    {
+        std::lock_guard<std::mutex> g(k->mu);
+        if (woks_locked(k, u.data(), xin.data(), mu, 1)) die("tfhe_bootstrap_woKS_FFT");
+    }
+    std::memcpy(result->a, u.data(), N * 4);
+    result->b = u[N];
+    result->current_variance = 0.0;
+}
+extern "C" void lweKeySwitch(LweSample *result, const LweKeySwitchKey *ks, const LweSample *sample) {
+    b200_key *k = lookup(g_by_ks, ks);
+    if (!k) { fail("key-switch key unknown: call b200_cloudkey_upload on its cloud key first"); die("lweKeySwitch"); }
+    const int n = k->dk.n, N = k->dk.N;
+    std::vector<int32_t> u(N + 1), out(n + 1);
+    int32_t nz = 0;
+    std::memcpy(u.data(), sample->a, N * 4);
+    u[N] = sample->b;
+    {
+        std::lock_guard<std::mutex> g(k->mu);
+        if (keyswitch_locked(k, out.data(), u.data(), &nz, 1)) die("lweKeySwitch");
+    }
+    std::memcpy(result->a, out.data(), n * 4);
+    result->b = out[n];
+    result->current_variance = nz * k->dk.ks_variance;
+}
+extern "C" void tfhe_bootstrap_FFT(LweSample *result, const LweBootstrappingKeyFFT *bk, Torus32 mu, const LweSample *x) {
+    b200_key *k = lookup(g_by_bkfft, bk);
+    if (!k) { fail("bootstrapping key unknown: call b200_cloudkey_upload on its cloud key first"); die("tfhe_bootstrap_FFT"); }
+    const int n = k->dk.n, N = k->dk.N;
+    std::vector<int32_t> xin(n + 1), u(N + 1), out(n + 1);
+    int32_t nz = 0;
+    std::memcpy(xin.data(), x->a, n * 4);
+    xin[n] = x->b;
+    {
+        std::lock_guard<std::mutex> g(k->mu);
+        if (woks_locked(k, u.data(), xin.data(), mu, 1)) die("tfhe_bootstrap_FFT");
+        if (keyswitch_locked(k, out.data(), u.data(), &nz, 1)) die("tfhe_bootstrap_FFT");
+    }
+    std::memcpy(result->a, out.data(), n * 4);
+    result->b = out[n];
+    result->current_variance = nz * k->dk.ks_variance;
+}

@@ -1,0 +1,70 @@
+// engine.cuh -- internal C++ interface between the C ABI (abi.cpp) and the CUDA kernels (kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace b200 {
+
+// Rotation-item descriptor for netlists (one blind rotation): x = cst + s0*W[w0] + s1*W[w1]
+struct RotDesc {
+    int32_t w0, w1;   // wire indices into the pool (w1 < 0: unused)
+    int32_t s0s1;     // (s0 & 0xffff) | (s1 << 16), signed 16-bit each
+    int32_t cst;      // added to the b term
+};
+// Key-switch item descriptor: out_wire <- KS( (0,add_b) + U[u0] (+ U[u1]) )
+struct KsDesc {
+    int32_t u0, u1;   // rows of the extracted buffer (u1 < 0: unused)
+    int32_t add_b;
+    int32_t out;      // destination row (wire index or batch row)
+};
+
+struct DeviceKey {
+    int n, N, k, l, Bgbit, ks_t, ks_basebit;
+    int ks_stride;            // n+1 rounded up to a multiple of 4 (int4 loads)
+    double ks_variance;
+    double2 *bkfft;           // [n][kpl][k+1][8][64]  evaluation domain, pass-3 layout
+    int32_t *ks;              // [N*k][t][base-1][ks_stride]
+    size_t bkfft_bytes, ks_bytes;
+    int device;
+};
+
+struct BlindRotateArgs {
+    // implicit batch form (desc == nullptr): item g uses rows g of in0/in1/in2 and `op`
+    const int32_t *in0, *in1, *in2;
+    int op;                   // b200_gate_op, or kOpRaw: x = in0[g] as is
+    // descriptor form
+    const RotDesc *desc;
+    const int32_t *pool;      // wires [*, n+1]
+    int32_t mu;               // test-vector value (2^29 for gates)
+    int32_t *u;               // out: [items][N+1]
+    int64_t items;
+};
+constexpr int kOpRaw = 100;
+
+struct KeySwitchArgs {
+    const int32_t *u;         // [*, N+1]
+    const KsDesc *desc;       // nullptr: item g reads row g (pair==0) or rows 2g,2g+1 (+2^29) (pair==1)
+    int pair;
+    int32_t *out;             // rows of n+1
+    int32_t *nonzero;         // optional per-item count of non-zero digits
+    int64_t items;
+};
+
+// host-callable launchers (kernels.cu)
+cudaError_t upload_twiddles();
+cudaError_t launch_bk_convert(const DeviceKey &key, const int32_t *d_bk_coefs, cudaStream_t s);
+cudaError_t launch_ks_pack(const DeviceKey &key, const int32_t *d_ks_rows, cudaStream_t s);
+cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s);
+cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaStream_t s);
+// mode 0: acc <- acc + BK_i (x) ((X^a - 1) acc)   mode 1: acc <- BK_i (x) acc
+cudaError_t launch_cmux_test(const DeviceKey &key, int32_t *d_acc, int bk_index, int barai, int mode,
+                             int64_t count, cudaStream_t s);
+// linear gates on device batches: out = s*in (+cst on b)
+cudaError_t launch_linear(const DeviceKey &key, int32_t *d_out, const int32_t *d_in, int sign, int32_t cst,
+                          int64_t count, cudaStream_t s);
+cudaError_t launch_linear_desc(const DeviceKey &key, int32_t *pool, const int32_t *d_desc /*[items][4]: op,out,in,unused*/,
+                               int64_t items, cudaStream_t s);
+int64_t launch_count();
+
+}  // namespace b200

@@ -1,0 +1,570 @@
+// kernels.cu -- sm_100a kernels of the gate-bootstrapping path.
+//
+//   k_bk_convert     one-time: integer bootstrapping key -> evaluation domain, coalesced layout
+//                    (replaces init_LweBootstrappingKeyFFT / tGswToFFTConvert,
+//                     libs/tfhe/src/libtfhe/lwe-bootstrapping-functions-fft.cpp:23-52,
+//                     tgsw-fft-operations.cpp:49-54)
+//   k_blind_rotate   gate prologue + modswitch + n CMux steps + sample extract, one ciphertext per
+//                    64-thread CTA, everything on chip
+//                    (boot-gates.cpp:35-370 prologues, lwe-bootstrapping-functions-fft.cpp:67-200,
+//                     tgsw-fft-operations.cpp:89-114, tgsw-functions.cpp:298-348, lwe.cpp:41-60)
+//   k_keyswitch      integer gather-accumulate over the key-switch table, batch tiled
+//                    (lwe-keyswitch-functions.cpp:114-129,228-238)
+//   k_cmux_test      a single CMux step / external product on caller accumulators (parity tests)
+#include "engine.cuh"
+#include "negacyclic_fft.cuh"
+#include "../../include/b200tfhe.h"
+
+#include <atomic>
+#include <math.h>
+
+namespace b200 {
+
+static std::atomic<int64_t> g_launches{0};
+int64_t launch_count() { return g_launches.load(); }
+#define COUNT_LAUNCH() g_launches.fetch_add(1, std::memory_order_relaxed)
+
+// ------------------------------------------------------------------------------------------------
+// twiddles: theta(level, b) = (pi/2 + 2 pi brv_level(b)) / 2^level is the argument of the root R of
+// the block modulus X^n - R; a butterfly of that block multiplies by sqrt(R) = e^{i theta/2}.
+// ------------------------------------------------------------------------------------------------
+static unsigned bit_reverse(unsigned v, int bits) {
+    unsigned r = 0;
+    for (int i = 0; i < bits; ++i) r |= ((v >> i) & 1u) << (bits - 1 - i);
+    return r;
+}
+static long double block_theta(int level, unsigned b) {
+    const long double pi = 3.14159265358979323846264338327950288L;
+    return (pi / 2 + 2 * pi * (long double)bit_reverse(b, level)) / (long double)(1u << level);
+}
+static double2 cos_tan(long double angle) {
+    return make_double2((double)cosl(angle), (double)tanl(angle));
+}
+static RootSet make_rootset(int level, unsigned b) {
+    const long double pi = 3.14159265358979323846264338327950288L;
+    RootSet w;
+    const long double c = block_theta(level + 2, 4 * b) / 2;
+    w.A = cos_tan(block_theta(level, b) / 2);
+    w.B = cos_tan(block_theta(level + 1, 2 * b) / 2);
+    w.C = cos_tan(c);
+    w.D = cos_tan(c + pi / 4);
+    return w;
+}
+cudaError_t upload_twiddles() {
+    static TwiddleTables h;
+    h.p1 = make_rootset(0, 0);
+    for (unsigned b = 0; b < 8; ++b) h.p2[b] = make_rootset(3, b);
+    for (unsigned b = 0; b < 64; ++b) h.p3[b] = make_rootset(6, b);
+    return cudaMemcpyToSymbol(c_tw, &h, sizeof(h));
+}
+
+// ------------------------------------------------------------------------------------------------
+// one-time key conversion
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64) k_bk_convert(const int32_t *__restrict__ coefs, double2 *__restrict__ out) {
+    __shared__ double2 buf[kBufElems];
+    const int t = threadIdx.x;
+    const int32_t *p = coefs + (size_t)blockIdx.x * kN;
+    double2 x[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+        x[r] = make_double2((double)p[t + 64 * r], (double)p[t + 64 * r + kM]);
+    const RootSet w2 = load_rootset(c_tw.p2[t >> 3]), w3 = load_rootset(c_tw.p3[t]);
+    negacyclic_forward(x, buf, t, w2, w3, CtaBarrier());
+    double2 *o = out + (size_t)blockIdx.x * kM;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) o[r * 64 + t] = x[r];
+}
+
+__global__ void k_ks_pack(const int32_t *__restrict__ rows, int32_t *__restrict__ out, int n1, int stride,
+                          int base, size_t nrows_out) {
+    // rows: [N*t][base][n1]  ->  out: [N*t][base-1][stride]
+    const size_t total = nrows_out * (size_t)stride;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (size_t)gridDim.x * blockDim.x) {
+        const size_t row = idx / stride;
+        const int col = (int)(idx - row * stride);
+        const size_t ij = row / (base - 1);
+        const int h = (int)(row - ij * (base - 1)) + 1;
+        out[idx] = col < n1 ? rows[(ij * base + h) * (size_t)n1 + col] : 0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// gate prologue coefficients: x = (0, cst) + s0*in_a + s1*in_b   (boot-gates.cpp:42,68,94,120,146,
+// 205,231,257,283,309 and :343-355 for the two halves of MUX)
+// ------------------------------------------------------------------------------------------------
+__host__ __device__ __forceinline__ void gate_coeffs(int op, int half, int &s0, int &s1, int32_t &cst, int &second) {
+    const int32_t e8 = 1 << 29, e4 = 1 << 30;
+    second = 1;
+    switch (op) {
+        case B200_NAND:  s0 = -1; s1 = -1; cst = e8;  break;
+        case B200_OR:    s0 = 1;  s1 = 1;  cst = e8;  break;
+        case B200_AND:   s0 = 1;  s1 = 1;  cst = -e8; break;
+        case B200_XOR:   s0 = 2;  s1 = 2;  cst = e4;  break;
+        case B200_XNOR:  s0 = -2; s1 = -2; cst = -e4; break;
+        case B200_NOR:   s0 = -1; s1 = -1; cst = -e8; break;
+        case B200_ANDNY: s0 = -1; s1 = 1;  cst = -e8; break;
+        case B200_ANDYN: s0 = 1;  s1 = -1; cst = -e8; break;
+        case B200_ORNY:  s0 = -1; s1 = 1;  cst = e8;  break;
+        case B200_ORYN:  s0 = 1;  s1 = -1; cst = e8;  break;
+        case B200_MUX:
+            if (half == 0) { s0 = 1; s1 = 1; cst = -e8; second = 1; }
+            else           { s0 = -1; s1 = 1; cst = -e8; second = 2; }
+            break;
+        default:         s0 = 1;  s1 = 0;  cst = 0;   break;  // kOpRaw
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// one CMux step on a shared-memory accumulator, executed by one 64-thread group
+//   MODE 0: ACC <- ACC + BK_i (x) ((X^a - 1) ACC)      (lwe-bootstrapping-functions-fft.cpp:67-76)
+//   MODE 1: ACC <- BK_i (x) ACC                         (tgsw-fft-operations.cpp:89-114)
+// ------------------------------------------------------------------------------------------------
+template <int L, int BGBIT, int MODE, class Barrier>
+__device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int a, const double2 *__restrict__ bk_i,
+                                          const int t, const RootSet &w2, const RootSet &w3, const Barrier &bar) {
+    constexpr uint32_t BG = 1u << BGBIT, HALF = BG >> 1, MASK = BG - 1;
+    uint32_t offset = 0;  // tgsw.cpp:7-29
+#pragma unroll
+    for (int p = 0; p < L; ++p) offset += HALF << (32 - (p + 1) * BGBIT);
+
+    double2 acc0[8], acc1[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) acc0[r] = acc1[r] = make_double2(0.0, 0.0);
+
+    int toggle = 0;
+#pragma unroll 1
+    for (int q = 0; q < 2; ++q) {
+        const int32_t *P = ACC + q * kN;
+        uint32_t dv[16];  // (rotated difference) + decomposition offset, coefficient t + 64 rr
+#pragma unroll
+        for (int rr = 0; rr < 16; ++rr) {
+            const int j = t + 64 * rr;
+            if (MODE == 0) {
+                const int m = (j - a) & (2 * kN - 1);
+                int32_t v = P[m & (kN - 1)];
+                if (m & kN) v = -v;
+                dv[rr] = (uint32_t)(v - P[j]) + offset;
+            } else {
+                dv[rr] = (uint32_t)P[j] + offset;
+            }
+        }
+#pragma unroll 1
+        for (int p = 0; p < L; ++p) {
+            const int shift = 32 - (p + 1) * BGBIT;
+            double2 x[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                const int32_t dre = (int32_t)((dv[r] >> shift) & MASK) - (int32_t)HALF;
+                const int32_t dim = (int32_t)((dv[r + 8] >> shift) & MASK) - (int32_t)HALF;
+                x[r] = make_double2(int_to_double(dre), int_to_double(dim));
+            }
+            negacyclic_forward(x, bufs + toggle * kBufElems, t, w2, w3, bar);
+            toggle ^= 1;
+            const double2 *row = bk_i + (size_t)(q * L + p) * 2 * kM + t;
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                const double2 b0 = __ldg(row + r * 64);
+                const double2 b1 = __ldg(row + kM + r * 64);
+                acc0[r].x = fma(x[r].x, b0.x, acc0[r].x);
+                acc0[r].x = fma(-x[r].y, b0.y, acc0[r].x);
+                acc0[r].y = fma(x[r].x, b0.y, acc0[r].y);
+                acc0[r].y = fma(x[r].y, b0.x, acc0[r].y);
+                acc1[r].x = fma(x[r].x, b1.x, acc1[r].x);
+                acc1[r].x = fma(-x[r].y, b1.y, acc1[r].x);
+                acc1[r].y = fma(x[r].x, b1.y, acc1[r].y);
+                acc1[r].y = fma(x[r].y, b1.x, acc1[r].y);
+            }
+        }
+    }
+    constexpr double kScale = 1.0 / kM;
+    negacyclic_inverse(acc0, bufs + toggle * kBufElems, t, w2, w3, bar);
+    toggle ^= 1;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const int j = t + 64 * r;
+        const int32_t lo = round_scaled_to_torus(acc0[r].x, kScale), hi = round_scaled_to_torus(acc0[r].y, kScale);
+        if (MODE == 0) { ACC[j] += lo; ACC[j + kM] += hi; }
+        else           { ACC[j] = lo;  ACC[j + kM] = hi; }
+    }
+    negacyclic_inverse(acc1, bufs + toggle * kBufElems, t, w2, w3, bar);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const int j = kN + t + 64 * r;
+        const int32_t lo = round_scaled_to_torus(acc1[r].x, kScale), hi = round_scaled_to_torus(acc1[r].y, kScale);
+        if (MODE == 0) { ACC[j] += lo; ACC[j + kM] += hi; }
+        else           { ACC[j] = lo;  ACC[j + kM] = hi; }
+    }
+    bar();  // accumulator complete before the next step's rotated reads
+}
+
+constexpr int kBrSmemBytes = 2 * kN * 4 + 2 * kBufElems * 16 + 1280;  // ACC + 2 exchange buffers + bara
+
+#ifndef BR_MAXREG
+#define BR_MAXREG 200
+#endif
+template <int L, int BGBIT>
+__global__ void __maxnreg__(BR_MAXREG) k_blind_rotate(const DeviceKey key, const BlindRotateArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    int32_t *ACC = reinterpret_cast<int32_t *>(smem);                         // [2][1024]
+    double2 *bufs = reinterpret_cast<double2 *>(smem + 2 * kN * 4);           // [2][576]
+    uint16_t *bara = reinterpret_cast<uint16_t *>(smem + 2 * kN * 4 + 2 * kBufElems * 16);  // [n+1]
+
+    const int t = threadIdx.x;
+    const int n = key.n, n1 = n + 1;
+    const int64_t item = blockIdx.x;
+
+    // ---- gate prologue + modulus switch to 2N (numeric-functions.cpp:59-65)
+    {
+        const int32_t *r0, *r1;
+        int s0, s1;
+        int32_t cst;
+        if (a.desc) {
+            const RotDesc d = a.desc[item];
+            r0 = a.pool + (size_t)d.w0 * n1;
+            r1 = d.w1 >= 0 ? a.pool + (size_t)d.w1 * n1 : r0;
+            s0 = (int16_t)(d.s0s1 & 0xffff);
+            s1 = d.w1 >= 0 ? (int16_t)(d.s0s1 >> 16) : 0;
+            cst = d.cst;
+        } else {
+            int second;
+            const int64_t gate = (a.op == B200_MUX) ? (item >> 1) : item;
+            gate_coeffs(a.op, (int)(item & 1), s0, s1, cst, second);
+            r0 = a.in0 + (size_t)gate * n1;
+            r1 = s1 ? ((second == 2 ? a.in2 : a.in1) + (size_t)gate * n1) : r0;
+        }
+        for (int i = t; i < n1; i += 64) {
+            uint32_t x = (uint32_t)s0 * (uint32_t)r0[i] + (uint32_t)s1 * (uint32_t)r1[i];
+            if (i == n) x += (uint32_t)cst;
+            bara[i] = (uint16_t)((x + 0x00100000u) >> 21);
+        }
+    }
+    __syncthreads();
+
+    // ---- ACC = (0, X^{2N-barb} * mu*(1+X+...+X^{N-1}))   (lwe-bootstrapping-functions-fft.cpp:146-148)
+    {
+        const int barb = bara[n];
+        const int32_t mu = a.mu;
+#pragma unroll
+        for (int rr = 0; rr < 16; ++rr) {
+            const int j = t + 64 * rr;
+            ACC[j] = 0;
+            ACC[kN + j] = ((j + barb) & kN) ? -mu : mu;
+        }
+    }
+    const RootSet w2 = load_rootset(c_tw.p2[t >> 3]), w3 = load_rootset(c_tw.p3[t]);
+    __syncthreads();
+
+    // ---- blind rotation (lwe-bootstrapping-functions-fft.cpp:88-112)
+    const size_t bk_stride = (size_t)2 * L * 2 * kM;  // double2 per TGSW sample
+#pragma unroll 1
+    for (int i = 0; i < n; ++i) {
+        const int ai = bara[i];
+        if (ai == 0) continue;
+        cmux_step<L, BGBIT, 0>(ACC, bufs, ai, key.bkfft + (size_t)i * bk_stride, t, w2, w3, CtaBarrier());
+    }
+
+    // ---- sample extract at index 0 (lwe.cpp:41-60)
+    int32_t *u = a.u + (size_t)item * (kN + 1);
+#pragma unroll
+    for (int rr = 0; rr < 16; ++rr) {
+        const int j = t + 64 * rr;
+        u[j] = (j == 0) ? ACC[0] : -ACC[kN - j];
+    }
+    if (t == 0) u[kN] = ACC[kN];
+}
+
+template <int L, int BGBIT>
+__global__ void __launch_bounds__(64, 6) k_cmux_test(const DeviceKey key, int32_t *acc, int bk_index, int barai, int mode) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    int32_t *ACC = reinterpret_cast<int32_t *>(smem);
+    double2 *bufs = reinterpret_cast<double2 *>(smem + 2 * kN * 4);
+    const int t = threadIdx.x;
+    int32_t *g = acc + (size_t)blockIdx.x * 2 * kN;
+    for (int j = t; j < 2 * kN; j += 64) ACC[j] = g[j];
+    const RootSet w2 = load_rootset(c_tw.p2[t >> 3]), w3 = load_rootset(c_tw.p3[t]);
+    __syncthreads();
+    const double2 *bk_i = key.bkfft + (size_t)bk_index * (2 * L * 2 * kM);
+    if (mode == 0) {
+        if (barai != 0) cmux_step<L, BGBIT, 0>(ACC, bufs, barai, bk_i, t, w2, w3, CtaBarrier());
+    } else {
+        cmux_step<L, BGBIT, 1>(ACC, bufs, 0, bk_i, t, w2, w3, CtaBarrier());
+    }
+    __syncthreads();
+    for (int j = t; j < 2 * kN; j += 64) g[j] = ACC[j];
+}
+
+// ------------------------------------------------------------------------------------------------
+// key switch, base 4 (basebit 2): tile of TB ciphertexts per CTA, one int4 column group per thread,
+// the three non-zero rows of (i,j) are loaded once per tile and selected by each ciphertext's digit.
+// grid = (tiles, i-splits); with more than one split the partial sums are combined with integer
+// atomics (wrap-around addition is associative, so the result is bit-exact in any order).
+// ------------------------------------------------------------------------------------------------
+constexpr int kKsTile = 8;
+
+template <int T>
+__global__ void __launch_bounds__(160) k_keyswitch(const DeviceKey key, const KeySwitchArgs a, int i_per_split, int nsplit) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    uint16_t *dig = reinterpret_cast<uint16_t *>(smem);  // [kKsTile][i_per_split]
+    __shared__ int nz[kKsTile];
+    __shared__ int32_t bterm[kKsTile];
+    __shared__ int32_t outrow[kKsTile];
+
+    const int Nin = key.N * key.k, n1 = key.n + 1, stride = key.ks_stride;
+    const int64_t item0 = (int64_t)blockIdx.x * kKsTile;
+    const int split = blockIdx.y;
+    const int i0 = split * i_per_split;
+    const int icnt = min(i_per_split, Nin - i0);
+    const uint32_t prec_offset = 1u << (32 - (1 + 2 * T));
+
+    if (threadIdx.x < kKsTile) {
+        const int g = threadIdx.x;
+        nz[g] = 0;
+        const int64_t item = item0 + g;
+        int32_t b = 0, orow = -1;
+        if (item < a.items) {
+            int64_t u0, u1 = -1;
+            int32_t add = 0;
+            if (a.desc) { const KsDesc d = a.desc[item]; u0 = d.u0; u1 = d.u1; add = d.add_b; orow = d.out; }
+            else if (a.pair) { u0 = 2 * item; u1 = 2 * item + 1; add = 1 << 29; orow = (int32_t)item; }
+            else { u0 = item; orow = (int32_t)item; }
+            b = a.u[u0 * (Nin + 1) + Nin] + add;
+            if (u1 >= 0) b += a.u[u1 * (Nin + 1) + Nin];
+        }
+        bterm[g] = b;
+        outrow[g] = orow;
+    }
+    __syncthreads();
+    // digit pre-pass (lwe-keyswitch-functions.cpp:122-125): top 2T bits of a_i + prec_offset
+    for (int idx = threadIdx.x; idx < kKsTile * icnt; idx += blockDim.x) {
+        const int g = idx / icnt, ii = idx - g * icnt;
+        const int64_t item = item0 + g;
+        uint32_t packed = 0;
+        if (item < a.items) {
+            int64_t u0, u1 = -1;
+            if (a.desc) { const KsDesc d = a.desc[item]; u0 = d.u0; u1 = d.u1; }
+            else if (a.pair) { u0 = 2 * item; u1 = 2 * item + 1; }
+            else u0 = item;
+            uint32_t v = (uint32_t)a.u[u0 * (Nin + 1) + i0 + ii];
+            if (u1 >= 0) v += (uint32_t)a.u[u1 * (Nin + 1) + i0 + ii];
+            packed = (v + prec_offset) >> (32 - 2 * T);
+            const int c = __popc((packed | (packed >> 1)) & 0x5555u);
+            if (c && a.nonzero) atomicAdd(&nz[g], c);
+        }
+        dig[g * i_per_split + ii] = (uint16_t)packed;
+    }
+    __syncthreads();
+
+    const int col4 = threadIdx.x;
+    const int stride4 = stride >> 2;
+    if (col4 < stride4) {
+        int4 acc[kKsTile];
+#pragma unroll
+        for (int g = 0; g < kKsTile; ++g) acc[g] = make_int4(0, 0, 0, 0);
+        const int4 *tab = reinterpret_cast<const int4 *>(key.ks) + (size_t)i0 * T * 3 * stride4 + col4;
+#pragma unroll 1
+        for (int ii = 0; ii < icnt; ++ii) {
+            int4 r[T][3];
+#pragma unroll
+            for (int j = 0; j < T; ++j)
+#pragma unroll
+                for (int h = 0; h < 3; ++h) r[j][h] = __ldg(tab + (size_t)((ii * T + j) * 3 + h) * stride4);
+#pragma unroll
+            for (int g = 0; g < kKsTile; ++g) {
+                const uint32_t pk = dig[g * i_per_split + ii];
+#pragma unroll
+                for (int j = 0; j < T; ++j) {
+                    const uint32_t d = (pk >> (2 * (T - 1 - j))) & 3u;
+                    if (d) {  // warp-uniform
+                        const int4 v = d == 1 ? r[j][0] : (d == 2 ? r[j][1] : r[j][2]);
+                        acc[g].x -= v.x; acc[g].y -= v.y; acc[g].z -= v.z; acc[g].w -= v.w;
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < kKsTile; ++g) {
+            const int orow = outrow[g];
+            if (orow < 0) continue;
+            int32_t *o = a.out + (size_t)orow * n1;
+            const int32_t vals[4] = {acc[g].x, acc[g].y, acc[g].z, acc[g].w};
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int col = col4 * 4 + c;
+                if (col < n1) {
+                    int32_t v = vals[c];
+                    if (col == key.n && split == 0) v += bterm[g];
+                    if (nsplit == 1) o[col] = v;
+                    else atomicAdd(o + col, v);
+                }
+            }
+        }
+    }
+    if (a.nonzero && threadIdx.x < kKsTile && item0 + threadIdx.x < a.items && nz[threadIdx.x])
+        atomicAdd(a.nonzero + item0 + threadIdx.x, nz[threadIdx.x]);
+}
+
+// zero the destination rows of a descriptor-driven key switch (needed when splits use atomics)
+__global__ void k_zero_rows(int32_t *out, const KsDesc *desc, int64_t items, int n1) {
+    const int64_t item = blockIdx.x;
+    if (item >= items) return;
+    const int64_t row = desc ? desc[item].out : item;
+    for (int c = threadIdx.x; c < n1; c += blockDim.x) out[row * n1 + c] = 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// linear gates (boot-gates.cpp:164-189): NOT = negate, COPY, CONSTANT = trivial +-1/8
+// ------------------------------------------------------------------------------------------------
+__global__ void k_linear(int32_t *out, const int32_t *in, int sign, int32_t cst, int n1, int64_t total) {
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        const int col = (int)(idx % n1);
+        int32_t v = in ? sign * in[idx] : 0;
+        if (col == n1 - 1) v += cst;
+        out[idx] = v;
+    }
+}
+__global__ void k_linear_desc(int32_t *pool, const int32_t *desc, int n1) {
+    const int32_t *d = desc + (size_t)blockIdx.x * 4;
+    const int op = d[0];
+    int32_t *o = pool + (size_t)d[1] * n1;
+    const int32_t *in = d[2] >= 0 ? pool + (size_t)d[2] * n1 : nullptr;
+    for (int c = threadIdx.x; c < n1; c += blockDim.x) {
+        int32_t v;
+        if (op == B200_NOT) v = -in[c];
+        else if (op == B200_COPY) v = in[c];
+        else v = (c == n1 - 1) ? (op == B200_CONST1 ? (1 << 29) : -(1 << 29)) : 0;
+        o[c] = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------------
+#define DISPATCH_L_BG(FN, ...)                                                      \
+    do {                                                                            \
+        if (key.l == 2 && key.Bgbit == 10) { FN<2, 10> __VA_ARGS__; }               \
+        else if (key.l == 3 && key.Bgbit == 7) { FN<3, 7> __VA_ARGS__; }            \
+        else if (key.l == 2 && key.Bgbit == 8) { FN<2, 8> __VA_ARGS__; }            \
+        else if (key.l == 1 && key.Bgbit == 16) { FN<1, 16> __VA_ARGS__; }          \
+        else if (key.l == 4 && key.Bgbit == 6) { FN<4, 6> __VA_ARGS__; }            \
+        else return cudaErrorInvalidValue;                                          \
+    } while (0)
+
+template <int L, int BGBIT>
+static cudaError_t set_br_attr() {
+    static bool done[16] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 16 && done[dev]) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(k_blind_rotate<L, BGBIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBrSmemBytes);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_cmux_test<L, BGBIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBrSmemBytes);
+    if (e != cudaSuccess) return e;
+    cudaFuncSetAttribute(k_blind_rotate<L, BGBIT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    if (dev < 16) done[dev] = true;
+    return cudaSuccess;
+}
+
+cudaError_t launch_bk_convert(const DeviceKey &key, const int32_t *d_bk_coefs, cudaStream_t s) {
+    const int polys = key.n * (key.k + 1) * key.l * (key.k + 1);
+    k_bk_convert<<<polys, 64, 0, s>>>(d_bk_coefs, key.bkfft);
+    COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_ks_pack(const DeviceKey &key, const int32_t *d_ks_rows, cudaStream_t s) {
+    const int base = 1 << key.ks_basebit;
+    const size_t nrows = (size_t)key.N * key.k * key.ks_t * (base - 1);
+    k_ks_pack<<<148 * 8, 256, 0, s>>>(d_ks_rows, key.ks, key.n + 1, key.ks_stride, base, nrows);
+    COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
+    if (a.items <= 0) return cudaSuccess;
+    if (a.items > 0x7fffffffLL || key.n + 1 > 640) return cudaErrorInvalidValue;
+#define BR_LAUNCH(L_, B_)                                                                 \
+    do {                                                                                  \
+        cudaError_t e = set_br_attr<L_, B_>();                                            \
+        if (e != cudaSuccess) return e;                                                   \
+        k_blind_rotate<L_, B_><<<(unsigned)a.items, 64, kBrSmemBytes, s>>>(key, a);       \
+    } while (0)
+    if (key.l == 2 && key.Bgbit == 10) BR_LAUNCH(2, 10);
+    else if (key.l == 3 && key.Bgbit == 7) BR_LAUNCH(3, 7);
+    else if (key.l == 2 && key.Bgbit == 8) BR_LAUNCH(2, 8);
+    else if (key.l == 1 && key.Bgbit == 16) BR_LAUNCH(1, 16);
+    else if (key.l == 4 && key.Bgbit == 6) BR_LAUNCH(4, 6);
+    else return cudaErrorInvalidValue;
+#undef BR_LAUNCH
+    COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_cmux_test(const DeviceKey &key, int32_t *d_acc, int bk_index, int barai, int mode,
+                             int64_t count, cudaStream_t s) {
+    if (count <= 0) return cudaSuccess;
+#define CT_LAUNCH(L_, B_)                                                                 \
+    do {                                                                                  \
+        cudaError_t e = set_br_attr<L_, B_>();                                            \
+        if (e != cudaSuccess) return e;                                                   \
+        k_cmux_test<L_, B_><<<(unsigned)count, 64, kBrSmemBytes, s>>>(key, d_acc, bk_index, barai, mode); \
+    } while (0)
+    if (key.l == 2 && key.Bgbit == 10) CT_LAUNCH(2, 10);
+    else if (key.l == 3 && key.Bgbit == 7) CT_LAUNCH(3, 7);
+    else if (key.l == 2 && key.Bgbit == 8) CT_LAUNCH(2, 8);
+    else if (key.l == 1 && key.Bgbit == 16) CT_LAUNCH(1, 16);
+    else if (key.l == 4 && key.Bgbit == 6) CT_LAUNCH(4, 6);
+    else return cudaErrorInvalidValue;
+#undef CT_LAUNCH
+    COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaStream_t s) {
+    if (a.items <= 0) return cudaSuccess;
+    if (key.ks_basebit != 2 || key.ks_t != 8) return cudaErrorInvalidValue;  // both reference sets: t=8, base 4
+    const int Nin = key.N * key.k;
+    const int64_t tiles = (a.items + kKsTile - 1) / kKsTile;
+    // enough CTAs to fill 148 SMs several times over; small batches split the i range instead
+    int nsplit = 1;
+    while (tiles * nsplit < 148 * 4 && nsplit < 64) nsplit *= 2;
+    const int i_per_split = (Nin + nsplit - 1) / nsplit;
+    const int threads = ((key.ks_stride / 4) + 31) / 32 * 32;
+    if (threads > 160) return cudaErrorInvalidValue;
+    if (nsplit > 1) {
+        k_zero_rows<<<(unsigned)a.items, 128, 0, s>>>(a.out, a.desc, a.items, key.n + 1);
+        COUNT_LAUNCH();
+    }
+    const size_t smem = (size_t)kKsTile * i_per_split * sizeof(uint16_t);
+    dim3 grid((unsigned)tiles, nsplit);
+    k_keyswitch<8><<<grid, threads, smem, s>>>(key, a, i_per_split, nsplit);
+    COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_linear(const DeviceKey &key, int32_t *d_out, const int32_t *d_in, int sign, int32_t cst,
+                          int64_t count, cudaStream_t s) {
+    if (count <= 0) return cudaSuccess;
+    const int64_t total = count * (key.n + 1);
+    const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+    k_linear<<<blocks, 256, 0, s>>>(d_out, d_in, sign, cst, key.n + 1, total);
+    COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_linear_desc(const DeviceKey &key, int32_t *pool, const int32_t *d_desc, int64_t items, cudaStream_t s) {
+    if (items <= 0) return cudaSuccess;
+    k_linear_desc<<<(unsigned)items, 128, 0, s>>>(pool, d_desc, key.n + 1);
+    COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+}  // namespace b200
+
+namespace b200 {
+void b200_gate_coeffs(int op, int half, int *s0, int *s1, int32_t *cst, int *second) {
+    gate_coeffs(op, half, *s0, *s1, *cst, *second);
+}
+}  // namespace b200

@@ -1,0 +1,274 @@
+/*
+ * b200tfhe.h -- C ABI of libb200tfhe.so, a B200 (sm_100a) engine for the TFHE gate-bootstrapping
+ * path of libtfhe (tfhe/tfhe v1.1, vendored by EntityOfCode/eoc-tfhe under libs/tfhe).
+ *
+ * Three groups of entry points:
+ *   1. libtfhe drop-in symbols   -- the exact names/signatures of the reference gate API
+ *                                   (libs/tfhe/src/include/tfhe_gate_bootstrapping_functions.h:14-87),
+ *                                   so a program linked against libb200tfhe.so *before* libtfhe gets
+ *                                   GPU gates while keygen / encrypt / IO stay in libtfhe.
+ *   2. bootsGate_batch           -- the batched form of (1) over arrays of LweSample pointers.
+ *   3. b200_*                    -- key objects, contiguous host/device batches, the pieces of the
+ *                                   path (blind rotation, key switch, one CMux step) for parity
+ *                                   tests, and levelised circuits.
+ *
+ * Only plain pointers and sizes cross this boundary (no C++ / torch types).
+ * All `int`-returning functions return 0 on success, non-zero on failure; the message is
+ * available from b200_last_error().  The void libtfhe-named gates abort() with a message on
+ * failure, like the reference's die_dramatically (libs/tfhe/src/libtfhe/tfhe_gate_bootstrapping.cpp:11-15).
+ *
+ * There is no CPU fallback: every compute entry fails if no CUDA device is usable.
+ */
+#ifndef B200TFHE_H
+#define B200TFHE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------
+ * libtfhe-compatible data layouts.  These mirror (field order, types, padding) the reference
+ * structs so that pointers produced by libtfhe can be passed here unchanged.  Define
+ * B200TFHE_NO_LIBTFHE_TYPES before including this header when <tfhe.h> is also included.
+ * ------------------------------------------------------------------------------------------ */
+#ifndef B200TFHE_NO_LIBTFHE_TYPES
+typedef int32_t Torus32;                       /* libs/tfhe/src/include/tfhe_core.h:28 */
+
+struct LweParams {                             /* include/lweparams.h:8-19 */
+    int32_t n;
+    double  alpha_min;
+    double  alpha_max;
+};
+struct LweSample {                             /* include/lwesamples.h:9-19 */
+    Torus32 *a;                                /* n mask coefficients, own heap block */
+    Torus32  b;
+    double   current_variance;
+};
+struct TLweParams {                            /* include/tlwe.h:10-28 */
+    int32_t N;
+    int32_t k;
+    double  alpha_min;
+    double  alpha_max;
+    struct LweParams extracted_lweparams;
+};
+struct TGswParams {                            /* include/tgsw.h:10-32 */
+    int32_t  l;
+    int32_t  Bgbit;
+    int32_t  Bg;
+    int32_t  halfBg;
+    uint32_t maskMod;
+    const struct TLweParams *tlwe_params;
+    int32_t  kpl;
+    Torus32 *h;
+    uint32_t offset;
+};
+struct TorusPolynomial {                       /* include/polynomials.h:22-32 */
+    int32_t  N;
+    Torus32 *coefsT;
+};
+struct TLweSample {                            /* include/tlwe.h:47-63 */
+    struct TorusPolynomial *a;                 /* k+1 polynomials */
+    struct TorusPolynomial *b;                 /* alias of a[k] */
+    double  current_variance;
+    int32_t k;
+};
+struct TGswSample {                            /* include/tgsw.h:55-76 */
+    struct TLweSample  *all_sample;            /* (k+1)*l rows */
+    struct TLweSample **bloc_sample;
+    int32_t k;
+    int32_t l;
+};
+struct LweKeySwitchKey {                       /* include/lwekeyswitch.h:11-28 */
+    int32_t n;                                 /* input dimension (N*k) */
+    int32_t t;
+    int32_t basebit;
+    int32_t base;
+    const struct LweParams *out_params;
+    struct LweSample   *ks0_raw;
+    struct LweSample  **ks1_raw;
+    struct LweSample ***ks;                    /* ks[i][j][h] */
+};
+struct LweBootstrappingKey {                   /* include/lwebootstrappingkey.h:7-30 */
+    const struct LweParams  *in_out_params;
+    const struct TGswParams *bk_params;
+    const struct TLweParams *accum_params;
+    const struct LweParams  *extract_params;
+    struct TGswSample       *bk;               /* n TGSW samples, integer domain */
+    struct LweKeySwitchKey  *ks;
+};
+struct LweBootstrappingKeyFFT {                /* include/lwebootstrappingkey.h:36-59 */
+    const struct LweParams  *in_out_params;
+    const struct TGswParams *bk_params;
+    const struct TLweParams *accum_params;
+    const struct LweParams  *extract_params;
+    const void              *bkFFT;            /* FFT-processor private; never read here */
+    const struct LweKeySwitchKey *ks;
+};
+struct TFheGateBootstrappingParameterSet {     /* include/tfhe_gate_bootstrapping_structures.h:9-24 */
+    int32_t ks_t;
+    int32_t ks_basebit;
+    const struct LweParams  *in_out_params;
+    const struct TGswParams *tgsw_params;
+};
+struct TFheGateBootstrappingCloudKeySet {      /* include/tfhe_gate_bootstrapping_structures.h:26-42 */
+    const struct TFheGateBootstrappingParameterSet *params;
+    const struct LweBootstrappingKey    *bk;
+    const struct LweBootstrappingKeyFFT *bkFFT;
+};
+#ifndef __cplusplus
+typedef struct LweParams LweParams;
+typedef struct LweSample LweSample;
+typedef struct TFheGateBootstrappingParameterSet TFheGateBootstrappingParameterSet;
+typedef struct TFheGateBootstrappingCloudKeySet TFheGateBootstrappingCloudKeySet;
+#endif
+#endif /* B200TFHE_NO_LIBTFHE_TYPES */
+
+/* ------------------------------------------------------------------------------------------
+ * 1. libtfhe drop-in gate symbols (libs/tfhe/src/libtfhe/boot-gates.cpp:35-370).
+ *    `bk` is uploaded to the GPU on first use and cached by pointer (b200_cloudkey_upload does
+ *    it eagerly).  `result` may alias an input.  result->current_variance is written as
+ *    (#non-zero keyswitch digits) * variance-of-a-KS-row, as lweKeySwitch does
+ *    (libs/tfhe/src/libtfhe/lwe-functions.cpp:222-234).
+ * ------------------------------------------------------------------------------------------ */
+void bootsNAND (struct LweSample *result, const struct LweSample *ca, const struct LweSample *cb, const struct TFheGateBootstrappingCloudKeySet *bk);  /* boot-gates.cpp:35  */
+void bootsOR   (struct LweSample *result, const struct LweSample *ca, const struct LweSample *cb, const struct TFheGateBootstrappingCloudKeySet *bk);  /* boot-gates.cpp:61  */
+void bootsAND  (struct LweSample *result, const struct LweSample *ca, const struct LweSample *cb, const struct TFheGateBootstrappingCloudKeySet *bk);  /* boot-gates.cpp:87  */
+void bootsXOR  (struct LweSample *result, const struct LweSample *ca, const struct LweSample *cb, const struct TFheGateBootstrappingCloudKeySet *bk);  /* boot-gates.cpp:113 */
+void bootsXNOR (struct LweSample *result, const struct LweSample *ca, const struct LweSample *cb, const struct TFheGateBootstrappingCloudKeySet *bk);  /* boot-gates.cpp:139 */
+void bootsNOR  (struct LweSample *result, const struct LweSample *ca, const struct LweSample *cb, const struct TFheGateBootstrappingCloudKeySet *bk);  /* boot-gates.cpp:198 */
+void bootsANDNY(struct LweSample *result, const struct LweSample *ca, const struct LweSample *cb, const struct TFheGateBootstrappingCloudKeySet *bk);  /* boot-gates.cpp:224 */
+void bootsANDYN(struct LweSample *result, const struct LweSample *ca, const struct LweSample *cb, const struct TFheGateBootstrappingCloudKeySet *bk);  /* boot-gates.cpp:250 */
+void bootsORNY (struct LweSample *result, const struct LweSample *ca, const struct LweSample *cb, const struct TFheGateBootstrappingCloudKeySet *bk);  /* boot-gates.cpp:276 */
+void bootsORYN (struct LweSample *result, const struct LweSample *ca, const struct LweSample *cb, const struct TFheGateBootstrappingCloudKeySet *bk);  /* boot-gates.cpp:302 */
+void bootsMUX  (struct LweSample *result, const struct LweSample *a, const struct LweSample *b, const struct LweSample *c, const struct TFheGateBootstrappingCloudKeySet *bk); /* boot-gates.cpp:329 */
+void bootsNOT  (struct LweSample *result, const struct LweSample *ca, const struct TFheGateBootstrappingCloudKeySet *bk);                              /* boot-gates.cpp:164 */
+void bootsCOPY (struct LweSample *result, const struct LweSample *ca, const struct TFheGateBootstrappingCloudKeySet *bk);                              /* boot-gates.cpp:175 */
+void bootsCONSTANT(struct LweSample *result, int32_t value, const struct TFheGateBootstrappingCloudKeySet *bk);                                        /* boot-gates.cpp:185 */
+
+/* Lower-level public functions of the same path (include/tfhe.h:42-45, include/lwe-functions.h:79).
+ * They take the reference's LweBootstrappingKeyFFT / LweKeySwitchKey handles; the device key is
+ * found through the cloud key they belong to, which must have been passed to
+ * b200_cloudkey_upload() before. */
+void tfhe_bootstrap_FFT     (struct LweSample *result, const struct LweBootstrappingKeyFFT *bk, Torus32 mu, const struct LweSample *x);  /* lwe-bootstrapping-functions-fft.cpp:213 */
+void tfhe_bootstrap_woKS_FFT(struct LweSample *result, const struct LweBootstrappingKeyFFT *bk, Torus32 mu, const struct LweSample *x);  /* lwe-bootstrapping-functions-fft.cpp:169 */
+void lweKeySwitch           (struct LweSample *result, const struct LweKeySwitchKey *ks, const struct LweSample *sample);               /* lwe-keyswitch-functions.cpp:228 */
+
+/* ------------------------------------------------------------------------------------------
+ * 2. Batched gate over libtfhe samples (new).
+ *    Snapshot semantics: every input of the batch is read before any output is written, so
+ *    out[] may alias inputs.  b/c may be NULL when the op does not use them.
+ * ------------------------------------------------------------------------------------------ */
+enum b200_gate_op {
+    B200_NAND = 0, B200_OR = 1, B200_AND = 2, B200_XOR = 3, B200_XNOR = 4, B200_NOR = 5,
+    B200_ANDNY = 6, B200_ANDYN = 7, B200_ORNY = 8, B200_ORYN = 9,
+    B200_MUX = 10,                 /* out = a ? b : c  (two blind rotations, one key switch) */
+    B200_NOT = 11, B200_COPY = 12, /* linear, no bootstrap */
+    B200_CONST0 = 13, B200_CONST1 = 14,
+    B200_GATE_OP_COUNT = 15
+};
+
+int bootsGate_batch(int op, struct LweSample *const *out, const struct LweSample *const *a,
+                    const struct LweSample *const *b, const struct LweSample *const *c,
+                    int32_t count, const struct TFheGateBootstrappingCloudKeySet *bk);
+
+/* ------------------------------------------------------------------------------------------
+ * 3. b200_* : keys, contiguous batches, path pieces, circuits.
+ *    A ciphertext batch is int32 [count][n+1] row-major: a[0..n) then b (the order of the
+ *    reference's wire format, libs/tfhe/src/libtfhe/tfhe_io.cpp:101-107).
+ *    An extracted-dimension batch is int32 [count][N*k+1].
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_key b200_key;
+
+typedef struct b200_params {
+    int32_t n;          /* LWE dimension (500 | 630) */
+    int32_t N;          /* ring degree, must be 1024 (as in every reference FFT processor) */
+    int32_t k;          /* must be 1 */
+    int32_t l;          /* gadget length (2 | 3), 1..4 supported */
+    int32_t Bgbit;      /* log2 gadget base (10 | 7) */
+    int32_t ks_t;       /* key-switch digits (8) */
+    int32_t ks_basebit; /* key-switch log2 base (2) */
+    double  ks_variance;/* variance carried by every KS row (current_variance bookkeeping) */
+} b200_params;
+
+const char *b200_last_error(void);
+int  b200_device_count(void);
+int  b200_set_device(int device);            /* device used by subsequently created keys */
+
+/* Key from a live libtfhe cloud key (reads bk->bk[i].all_sample[p].a[q].coefsT and
+ * bk->ks->ks[i][j][h], cf. lwe-bootstrapping-functions-fft.cpp:23-52) -- converts the
+ * bootstrapping key to the FFT domain ON THE GPU and uploads the key-switch table. The handle is
+ * cached by `bk` pointer so that the drop-in gates find it. */
+int  b200_cloudkey_upload(const struct TFheGateBootstrappingCloudKeySet *bk, b200_key **out);
+void b200_cloudkey_forget(const struct TFheGateBootstrappingCloudKeySet *bk); /* frees the cached key */
+
+/* Key from raw integer arrays (what the wire format carries, tfhe_io.cpp:757-930):
+ *   bk_coefs : int32 [n][(k+1)*l][k+1][N]     bk[i].all_sample[row].a[col].coefsT
+ *   ks_rows  : int32 [N*k][t][base][n+1]       ks[i][j][h] as (a[0..n), b); h=0 rows are ignored */
+int  b200_key_create(const b200_params *p, const int32_t *bk_coefs, const int32_t *ks_rows, b200_key **out);
+/* Key with device storage allocated but not filled (multi-GPU: non-root ranks, then
+ * b200_key_device_blobs + a broadcast into them). */
+int  b200_key_create_empty(const b200_params *p, b200_key **out);
+void b200_key_free(b200_key *key);
+int  b200_key_params(const b200_key *key, b200_params *out);
+/* Device pointers/sizes of the two resident blobs: FFT-domain bootstrapping key and KS table. */
+int  b200_key_device_blobs(const b200_key *key, void **d_bkfft, size_t *bkfft_bytes,
+                           void **d_ks, size_t *ks_bytes);
+
+/* Gates on contiguous HOST batches (H2D + kernels + D2H inside the call). */
+int  b200_gate_batch_host(b200_key *key, int op, int32_t *out, const int32_t *a, const int32_t *b,
+                          const int32_t *c, int64_t count);
+/* Gates on DEVICE-resident batches; `stream` is a cudaStream_t (NULL = default stream).
+ * Asynchronous: returns after enqueueing. out must not overlap inputs. */
+int  b200_gate_batch_dev(b200_key *key, int op, int32_t *d_out, const int32_t *d_a,
+                         const int32_t *d_b, const int32_t *d_c, int64_t count, void *stream);
+
+/* Pieces of the path, for parity tests and for callers that hold extracted samples. */
+/* u[count][N+1] = tfhe_bootstrap_woKS_FFT(x[count][n+1], mu)       (fft.cpp:169-200) */
+int  b200_bootstrap_woks_host(b200_key *key, int32_t *u, const int32_t *x, int32_t mu, int64_t count);
+/* out[count][n+1] = lweKeySwitch(u[count][N+1]); nonzero_digits[count] optional (may be NULL) */
+int  b200_keyswitch_host(b200_key *key, int32_t *out, const int32_t *u, int32_t *nonzero_digits, int64_t count);
+int  b200_keyswitch_dev (b200_key *key, int32_t *d_out, const int32_t *d_u, int64_t count, void *stream);
+/* One CMux step: acc[count][k+1][N] <- acc + BK_i (x) ((X^barai - 1) * acc)   (fft.cpp:67-76).
+ * With barai == 0 the accumulator is returned unchanged, as tfhe_blindRotate_FFT skips (fft.cpp:101). */
+int  b200_cmux_step_host(b200_key *key, int32_t *acc, int32_t bk_index, int32_t barai, int64_t count);
+/* tGswFFTExternMulToTLwe alone: acc[count][k+1][N] <- BK_i (x) acc   (tgsw-fft-operations.cpp:89-114) */
+int  b200_extern_product_host(b200_key *key, int32_t *acc, int32_t bk_index, int64_t count);
+
+/* Levelised circuits: a netlist over a pool of wires, all independent gates of
+ * one depth level run as one launch pair.
+ *   gates : int32 [num_gates][5] = {op, out_wire, in_a, in_b, in_c} (unused inputs = -1)
+ *   wires : int32 [num_wires][n+1] host pool, inputs pre-filled, outputs written back.
+ * Gates must be listed in a valid topological order; each wire is written at most once. */
+int  b200_circuit_run_host(b200_key *key, const int32_t *gates, int64_t num_gates,
+                           int32_t *wires, int64_t num_wires, int32_t *levels_out);
+int  b200_circuit_run_dev (b200_key *key, const int32_t *gates, int64_t num_gates,
+                           int32_t *d_wires, int64_t num_wires, int32_t *levels_out, void *stream);
+
+/* Host-only netlist helpers (no device needed): level of every gate (number of bootstrapped stages
+ * before its output is ready; linear gates share the level of their input) and validation. */
+int  b200_circuit_levelize(const int32_t *gates, int64_t num_gates, int64_t num_wires,
+                           int32_t *gate_level, int32_t *num_levels);
+/* Expand bootstrapped gates into launch descriptors:
+ *   rot_desc rows {w0, w1, s0 | s1<<16, cst}   x = (0,cst) + s0*W[w0] + s1*W[w1]   (MUX: two rows)
+ *   ks_desc  rows {u0, u1, add_b, out_wire}    out = KS((0,add_b) + U[u0] (+ U[u1])) */
+int  b200_expand_gates(const int32_t *gates, int64_t num_gates, int32_t *rot_desc, int64_t *n_rot,
+                       int32_t *ks_desc, int64_t *n_ks);
+/* One level given as descriptors (host arrays) over a device wire pool: one blind-rotation launch
+ * and one key-switch launch on `stream`. Used by multi-GPU drivers that shard a level by rank. */
+int  b200_level_run_dev(b200_key *key, int32_t *d_wires, const int32_t *rot_desc, int64_t n_rot,
+                        const int32_t *ks_desc, int64_t n_ks, void *stream);
+
+/* Timing helper: milliseconds of GPU time (cudaEvent, on the key's stream) spent in the kernels
+ * of the most recent *_host / *_dev call on this key: [0]=blind rotation, [1]=key switch,
+ * [2]=total incl. copies. Synchronises the stream. */
+int  b200_last_timing_ms(b200_key *key, float out_ms[3]);
+/* Number of kernels this library has launched since load (bench.py's gpu_launches). */
+int64_t b200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200TFHE_H */

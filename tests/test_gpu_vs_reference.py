@@ -1,0 +1,126 @@
+"""GPU path vs the UNMODIFIED reference (oracle/_ref/libtfhe-spqlios-fma.so) on the same keys.
+
+Parity protocol of SURVEY.md section 8c: (ii) key switch bit-exact, (iii) one external product /
+one CMux step within 2 LSB per coefficient of the reference's FP64 FFT result (and of the exact
+integer product), (i) decrypted gate outputs identical.
+"""
+import numpy as np
+import pytest
+
+import reflib
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(not reflib.available(), reason="oracle/_ref not built (needs /root/reference)")]
+
+
+@pytest.fixture(scope="module", params=[80, 128], ids=["P80", "P128"])
+def keys(request):
+    from eoc_tfhe_b200 import CloudKey
+    ref = reflib.RefLib()
+    rk = ref.keygen(request.param, seed=42)
+    ck = CloudKey.from_libtfhe(rk.cloud_ptr)
+    yield rk, ck
+    ck.close()
+
+
+def test_params_roundtrip(keys):
+    rk, ck = keys
+    p = ck.params
+    assert (p.n, p.N, p.k, p.l, p.Bgbit, p.ks_t, p.ks_basebit) == (rk.n, rk.N, rk.k, rk.l, rk.Bgbit, rk.ks_t, rk.ks_basebit)
+
+
+def test_keyswitch_bit_exact(keys):
+    rk, ck = keys
+    rng = np.random.default_rng(1)
+    u = rng.integers(-2**31, 2**31, size=(24, rk.N + 1), dtype=np.int64).astype(np.int32)
+    u[0] = 0                      # all digits hit the rounding offset only
+    u[1, :rk.N] = -1              # carries through every digit
+    u[2, :rk.N] = 0x7FFFFFFF
+    want, var = rk.keyswitch(u)
+    got, nz = ck.keyswitch(u, with_counts=True)
+    assert np.array_equal(got, want)
+    assert np.allclose(nz * rk.ks_variance(), var, rtol=1e-12, atol=0)
+
+
+def test_keyswitch_large_batch_matches_small(keys):
+    rk, ck = keys
+    rng = np.random.default_rng(2)
+    u = rng.integers(-2**31, 2**31, size=(700, rk.N + 1), dtype=np.int64).astype(np.int32)
+    big = ck.keyswitch(u)                      # tiles only
+    small = np.concatenate([ck.keyswitch(u[i:i + 7]) for i in range(0, 700, 7)])  # split-i + atomics
+    assert np.array_equal(big, small)
+    want, _ = rk.keyswitch(u[:8])
+    assert np.array_equal(big[:8], want)
+
+
+def test_extern_product_within_2lsb(keys):
+    rk, ck = keys
+    rng = np.random.default_rng(3)
+    acc = rng.integers(-2**31, 2**31, size=(4, 2, rk.N), dtype=np.int64).astype(np.int32)
+    for idx in (0, 1, rk.n - 1):
+        got = ck.extern_product(acc, idx)
+        for g in range(acc.shape[0]):
+            fft = rk.extern_product_fft(acc[g], idx)
+            exact = rk.extern_product_exact(acc[g], idx)
+            d_fft = np.abs((got[g].astype(np.int64) - fft.astype(np.int64) + 2**31) % 2**32 - 2**31)
+            d_exact = np.abs((got[g].astype(np.int64) - exact.astype(np.int64) + 2**31) % 2**32 - 2**31)
+            assert d_fft.max() <= 2, d_fft.max()      # bound on |GPU - reference FP64 FFT|, in 2^-32 units
+            assert d_exact.max() <= 2, d_exact.max()  # bound on |GPU - exact product|
+
+
+def test_cmux_step_within_2lsb(keys):
+    rk, ck = keys
+    rng = np.random.default_rng(4)
+    acc = rng.integers(-2**31, 2**31, size=(3, 2, rk.N), dtype=np.int64).astype(np.int32)
+    for barai in (1, 517, 1024, 1531, 2047):
+        got = ck.cmux_step(acc, 5, barai)
+        for g in range(acc.shape[0]):
+            want = rk.cmux_step(acc[g], 5, barai)
+            d = np.abs((got[g].astype(np.int64) - want.astype(np.int64) + 2**31) % 2**32 - 2**31)
+            assert d.max() <= 2, (barai, d.max())
+    assert np.array_equal(ck.cmux_step(acc, 5, 0), acc)  # barai == 0 is skipped (fft.cpp:101)
+
+
+def test_bootstrap_woks_phase(keys):
+    rk, ck = keys
+    rng = np.random.default_rng(5)
+    bits = rng.integers(0, 2, size=16)
+    x = rk.encrypt_bits(bits)
+    mu = 1 << 29
+    got = ck.bootstrap_woks(x, mu)
+    want = rk.bootstrap_woks(x, mu)
+    pg, pw = rk.phase_extracted(got), rk.phase_extracted(want)
+    sign = np.where(bits > 0, 1, -1)
+    assert np.all(np.abs(pg.astype(np.int64) - sign * mu) < 2**26)   # well inside the +-1/16 margin
+    assert np.all((pg > 0) == (pw > 0))
+
+
+GATE_TRUTH = {
+    "NAND": lambda a, b: 1 - (a & b), "OR": lambda a, b: a | b, "AND": lambda a, b: a & b,
+    "XOR": lambda a, b: a ^ b, "XNOR": lambda a, b: 1 - (a ^ b), "NOR": lambda a, b: 1 - (a | b),
+    "ANDNY": lambda a, b: (1 - a) & b, "ANDYN": lambda a, b: a & (1 - b),
+    "ORNY": lambda a, b: (1 - a) | b, "ORYN": lambda a, b: a | (1 - b),
+}
+
+
+def test_all_gates_decrypt_like_reference(keys):
+    from eoc_tfhe_b200 import GateOp
+    rk, ck = keys
+    rng = np.random.default_rng(6)
+    count = 8
+    a_bits, b_bits, c_bits = (rng.integers(0, 2, size=count) for _ in range(3))
+    a, b, c = rk.encrypt_bits(a_bits), rk.encrypt_bits(b_bits), rk.encrypt_bits(c_bits)
+    for name, fn in GATE_TRUTH.items():
+        got = ck.gate(GateOp[name], a, b)
+        want, _ = rk.gate(name, a[:2], b[:2])
+        assert np.array_equal(rk.decrypt_bits(got), fn(a_bits, b_bits)), name
+        assert np.array_equal(rk.decrypt_bits(want), fn(a_bits, b_bits)[:2]), name
+    got = ck.gate(GateOp.MUX, a, b, c)
+    assert np.array_equal(rk.decrypt_bits(got), np.where(a_bits > 0, b_bits, c_bits))
+    want, _ = rk.gate("MUX", a[:2], b[:2], c[:2])
+    assert np.array_equal(rk.decrypt_bits(want), np.where(a_bits > 0, b_bits, c_bits)[:2])
+    # linear gates are bit-exact
+    assert np.array_equal(ck.gate(GateOp.NOT, a), -a)
+    assert np.array_equal(ck.gate(GateOp.COPY, a), a)
+    one = ck.gate(GateOp.CONST1, out=np.empty_like(a))
+    assert np.all(one[:, :-1] == 0) and np.all(one[:, -1] == 1 << 29)
