@@ -155,6 +155,26 @@ class RefLib:
         sk = self.L.new_random_gate_bootstrapping_secret_keyset(params)
         return RefKeys(self, sk)
 
+    def keygen_custom(self, n, l, Bgbit, ks_t=8, ks_basebit=2, ks_stdev=2.44e-5, bk_stdev=7.18e-9,
+                      max_stdev=0.012467, seed=42):
+        """Keys for a non-default parameter set, built the way default_80bit_gate_bootstrapping_parameters
+        does (tfhe_gate_bootstrapping.cpp:23-48) -- used for SMALL golden fixtures (small n)."""
+        L = self.L
+        L.new_LweParams.restype = C.POINTER(LweParams)
+        L.new_LweParams.argtypes = [C.c_int32, C.c_double, C.c_double]
+        L.new_TLweParams.restype = C.POINTER(TLweParams)
+        L.new_TLweParams.argtypes = [C.c_int32, C.c_int32, C.c_double, C.c_double]
+        L.new_TGswParams.restype = C.POINTER(TGswParams)
+        L.new_TGswParams.argtypes = [C.c_int32, C.c_int32, C.c_void_p]
+        self.seed(seed)
+        p_in = L.new_LweParams(n, ks_stdev, max_stdev)
+        p_acc = L.new_TLweParams(1024, 1, bk_stdev, max_stdev)
+        p_bk = L.new_TGswParams(l, Bgbit, p_acc)
+        ps = ParameterSet(ks_t, ks_basebit, p_in, p_bk)
+        self._keep = getattr(self, "_keep", []) + [ps]
+        sk = L.new_random_gate_bootstrapping_secret_keyset(C.byref(ps))
+        return RefKeys(self, sk)
+
     def load_secret_keyset(self, path):
         f = self.libc.fopen(path.encode(), b"rb")
         sk = self.L.new_tfheGateBootstrappingSecretKeySet_fromFile(f)
@@ -326,12 +346,28 @@ class RefKeys:
         return out
 
     def extern_product_exact(self, acc, bk_index):
-        """tGswExternMulToTLwe (tgsw-functions.cpp:156-170): exact integer arithmetic."""
+        """External product in EXACT integer arithmetic from the reference's own pieces:
+        tGswTLweDecompH (tgsw-functions.cpp:353-360) + torusPolynomialAddMulRKaratsuba
+        (multiplication.cpp:146-160), summed like tGswExternMulToTLwe (tgsw-functions.cpp:156-170).
+        (tGswExternMulToTLwe itself multiplies through the FFT: polynomials_arithmetic.h:113.)"""
+        L = self.L
+        L.new_IntPolynomial_array.restype = C.POINTER(IntPolynomial)
+        L.new_IntPolynomial_array.argtypes = [C.c_int32, C.c_int32]
+        L.delete_IntPolynomial_array.argtypes = [C.c_int32, C.c_void_p]
+        L.tGswTLweDecompH.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.tLweClear.argtypes = [C.c_void_p, C.c_void_p]
+        L.torusPolynomialAddMulRKaratsuba.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         t = self._tlwe_from(np.ascontiguousarray(acc, dtype=np.int32))
-        bk = self.cloud.bk.contents.bk
-        self.L.tGswExternMulToTLwe(t, C.byref(bk[bk_index]), self.tgsw_params)
+        dec = L.new_IntPolynomial_array(self.kpl, self.N)
+        L.tGswTLweDecompH(dec, t, self.tgsw_params)
+        L.tLweClear(t, self.tlwe_params)
+        rows = self.cloud.bk.contents.bk[bk_index].all_sample
+        for i in range(self.kpl):
+            for c in range(self.k + 1):
+                L.torusPolynomialAddMulRKaratsuba(C.byref(t.contents.a[c]), C.byref(dec[i]), C.byref(rows[i].a[c]))
         out = self._tlwe_read(t)
-        self.L.delete_TLweSample(t)
+        L.delete_IntPolynomial_array(self.kpl, dec)
+        L.delete_TLweSample(t)
         return out
 
     def cmux_step(self, acc, bk_index, barai):
@@ -339,7 +375,7 @@ class RefKeys:
         src = self._tlwe_from(np.ascontiguousarray(acc, dtype=np.int32))
         dst = self.L.new_TLweSample(self.tlwe_params)
         bkfft = self.cloud.bkFFT.contents.bkFFT
-        self._muxrot(dst, src, C.c_void_p(bkfft + 24 * bk_index), int(barai), self.tgsw_params)
+        self.ref._muxrot(dst, src, C.c_void_p(bkfft + 24 * bk_index), int(barai), self.tgsw_params)
         out = self._tlwe_read(dst)
         self.L.delete_TLweSample(src)
         self.L.delete_TLweSample(dst)
