@@ -94,7 +94,8 @@ static int key_alloc(const b200_params *p, b200_key **out) {
     cudaError_t e = cudaMalloc((void **)&d.bkfft, d.bkfft_bytes);
     if (e == cudaSuccess) e = cudaMalloc((void **)&d.ks, d.ks_bytes);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking);
-    for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&k->ev[i]);
+    for (int i = 0; i < b200_key::kRing * 3 && e == cudaSuccess; ++i) e = cudaEventCreate(&k->ring[i / 3][i % 3]);
+    if (e == cudaSuccess) e = cudaEventCreate(&k->ev_start);
     if (e == cudaSuccess) e = upload_twiddles();
     if (e != cudaSuccess) {
         fail_cuda("key allocation", e);
@@ -155,8 +156,10 @@ extern "C" void b200_key_free(b200_key *k) {
     for (DevBuf *b : {&k->u, &k->in0, &k->in1, &k->in2, &k->out, &k->nz, &k->desc_rot, &k->desc_ks, &k->desc_lin, &k->acc}) b->release();
     k->stage_in.release();
     k->stage_out.release();
-    for (auto &e : k->ev)
-        if (e) cudaEventDestroy(e);
+    for (auto &slot : k->ring)
+        for (auto &e : slot)
+            if (e) cudaEventDestroy(e);
+    if (k->ev_start) cudaEventDestroy(k->ev_start);
     if (k->stream) cudaStreamDestroy(k->stream);
     delete k;
 }
@@ -273,9 +276,10 @@ static int enqueue_gates(b200_key *k, int op, int32_t *d_out, const int32_t *d_a
         br.u = (int32_t *)k->u.p;
         br.items = g * per;
         const bool t = timed && g0 == 0;
-        if (t) CK(cudaEventRecord(k->ev[0], s));
+        cudaEvent_t *ev = k->ring[k->ring_head % b200_key::kRing];
+        if (t) CK(cudaEventRecord(ev[0], s));
         CK(launch_blind_rotate(d, br, s));
-        if (t) CK(cudaEventRecord(k->ev[1], s));
+        if (t) CK(cudaEventRecord(ev[1], s));
         KeySwitchArgs ks{};
         ks.u = (const int32_t *)k->u.p;
         ks.pair = per == 2;
@@ -283,7 +287,10 @@ static int enqueue_gates(b200_key *k, int op, int32_t *d_out, const int32_t *d_a
         ks.nonzero = d_nonzero ? d_nonzero + g0 : nullptr;
         ks.items = g;
         CK(launch_keyswitch(d, ks, s));
-        if (t) CK(cudaEventRecord(k->ev[2], s));
+        if (t) {
+            CK(cudaEventRecord(ev[2], s));
+            k->ring_head++;
+        }
     }
     return 0;
 }
@@ -311,7 +318,7 @@ static int gate_batch_host_locked(b200_key *k, int op, int32_t *out, const int32
     const bool need_b = !op_is_linear(op);
     const bool need_c = op == B200_MUX;
     if ((need_a && !a) || (need_b && !b) || (need_c && !c) || !out) return fail("NULL batch pointer");
-    CK(cudaEventRecord(k->ev[3], s));
+    CK(cudaEventRecord(k->ev_start, s));
     if (need_a) { if (k->in0.ensure(bytes)) return 1; CK(cudaMemcpyAsync(k->in0.p, a, bytes, cudaMemcpyHostToDevice, s)); }
     if (need_b) { if (k->in1.ensure(bytes)) return 1; CK(cudaMemcpyAsync(k->in1.p, b, bytes, cudaMemcpyHostToDevice, s)); }
     if (need_c) { if (k->in2.ensure(bytes)) return 1; CK(cudaMemcpyAsync(k->in2.p, c, bytes, cudaMemcpyHostToDevice, s)); }
@@ -347,16 +354,46 @@ extern "C" int b200_last_timing_ms(b200_key *k, float out_ms[3]) {
     if (!k || !out_ms) return fail("NULL argument");
     std::lock_guard<std::mutex> g(k->mu);
     CK(cudaSetDevice(k->dk.device));
-    if (k->timing_pending) {
-        CK(cudaEventSynchronize(k->ev[2]));
-        CK(cudaEventElapsedTime(&k->last_ms[0], k->ev[0], k->ev[1]));
-        CK(cudaEventElapsedTime(&k->last_ms[1], k->ev[1], k->ev[2]));
+    if (k->timing_pending && k->ring_head > 0) {
+        cudaEvent_t *ev = k->ring[(k->ring_head - 1) % b200_key::kRing];
+        CK(cudaEventSynchronize(ev[2]));
+        CK(cudaEventElapsedTime(&k->last_ms[0], ev[0], ev[1]));
+        CK(cudaEventElapsedTime(&k->last_ms[1], ev[1], ev[2]));
         float tot = 0;
-        if (cudaEventElapsedTime(&tot, k->ev[3], k->ev[2]) == cudaSuccess) k->last_ms[2] = tot;
+        if (cudaEventElapsedTime(&tot, k->ev_start, ev[2]) == cudaSuccess && tot > 0) k->last_ms[2] = tot;
         else { cudaGetLastError(); k->last_ms[2] = k->last_ms[0] + k->last_ms[1]; }
         k->timing_pending = false;
     }
     out_ms[0] = k->last_ms[0]; out_ms[1] = k->last_ms[1]; out_ms[2] = k->last_ms[2];
+    return 0;
+}
+
+extern "C" int b200_timing_drain(b200_key *k, double sum_ms[2], int32_t *calls) {
+    if (!k || !sum_ms || !calls) return fail("NULL argument");
+    std::lock_guard<std::mutex> g(k->mu);
+    CK(cudaSetDevice(k->dk.device));
+    sum_ms[0] = sum_ms[1] = 0;
+    *calls = 0;
+    const int64_t begin = std::max(k->ring_drained, k->ring_head - b200_key::kRing);
+    for (int64_t c = begin; c < k->ring_head; ++c) {
+        cudaEvent_t *ev = k->ring[c % b200_key::kRing];
+        float a = 0, b = 0;
+        CK(cudaEventSynchronize(ev[2]));
+        CK(cudaEventElapsedTime(&a, ev[0], ev[1]));
+        CK(cudaEventElapsedTime(&b, ev[1], ev[2]));
+        sum_ms[0] += a;
+        sum_ms[1] += b;
+        ++*calls;
+    }
+    k->ring_drained = k->ring_head;
+    return 0;
+}
+
+extern "C" int b200_fp64_peak_tflops(int device, double *tflops) {
+    if (!tflops) return fail("NULL argument");
+    if (b200_device_count() <= 0) return fail("no CUDA device");
+    CK(cudaSetDevice(device));
+    CK(measure_fp64_peak(tflops));
     return 0;
 }
 

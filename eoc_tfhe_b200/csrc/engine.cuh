@@ -66,5 +66,6 @@ cudaError_t launch_linear(const DeviceKey &key, int32_t *d_out, const int32_t *d
 cudaError_t launch_linear_desc(const DeviceKey &key, int32_t *pool, const int32_t *d_desc /*[items][4]: op,out,in,unused*/,
                                int64_t items, cudaStream_t s);
 int64_t launch_count();
+cudaError_t measure_fp64_peak(double *tflops);
 
 }  // namespace b200

@@ -65,7 +65,11 @@ struct b200_key {
     std::mutex mu;                      // one call at a time per key (shared workspace)
     DevBuf u, in0, in1, in2, out, nz, desc_rot, desc_ks, desc_lin, acc;
     PinnedBuf stage_in, stage_out;
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    // ring of CUDA-event triplets (before blind rotation, between, after key switch), one per gate call
+    static constexpr int kRing = 64;
+    cudaEvent_t ring[kRing][3] = {};
+    int64_t ring_head = 0, ring_drained = 0;
+    cudaEvent_t ev_start = nullptr;     // start of the most recent *_host call (incl. copies)
     float last_ms[3] = {0, 0, 0};
     bool timing_pending = false;
 };

@@ -561,6 +561,52 @@ cudaError_t launch_linear_desc(const DeviceKey &key, int32_t *pool, const int32_
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------------------------
+// FP64 FMA peak of this GPU (roofline denominator of the blind rotation): 8 independent DFMA
+// chains per thread, 256 threads x 8 CTAs per SM, timed with CUDA events.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_fp64_peak(double *sink, int iters, double seed) {
+    double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const double m = 1.0 - 1e-9, c = 1e-9;
+#pragma unroll 1
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+            a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+        }
+    }
+    const double r = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+    if (r == 123.456) sink[0] = r;
+}
+cudaError_t measure_fp64_peak(double *tflops) {
+    double *sink = nullptr;
+    cudaError_t e = cudaMalloc(&sink, 8);
+    if (e != cudaSuccess) return e;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int blocks = 148 * 8, iters = 4096;
+    double best = 0;
+    for (int rep = 0; rep < 4; ++rep) {
+        cudaEventRecord(e0);
+        k_fp64_peak<<<blocks, 256>>>(sink, iters, 1.0);
+        COUNT_LAUNCH();
+        cudaEventRecord(e1);
+        e = cudaEventSynchronize(e1);
+        if (e != cudaSuccess) break;
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double flop = 2.0 * 64.0 * iters * 256.0 * blocks;
+        if (rep > 0 && ms > 0) best = fmax(best, flop / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(sink);
+    *tflops = best;
+    return e;
+}
+
 }  // namespace b200
 
 namespace b200 {

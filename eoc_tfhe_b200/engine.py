@@ -149,6 +149,23 @@ class CloudKey:
         _lib.check(_lib.load().b200_key_device_blobs(self._h, C.byref(a), C.byref(na), C.byref(b), C.byref(nb)))
         return [(a.value, na.value), (b.value, nb.value)]
 
+    def device_blob_tensors(self):
+        """The two resident blobs as zero-copy torch uint8 CUDA tensors (for dist.broadcast)."""
+        import torch
+
+        class _Raw:
+            def __init__(self, ptr, nbytes):
+                self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+        return [torch.as_tensor(_Raw(p, nb), device="cuda") for p, nb in self.device_blobs()]
+
+    def timing_drain(self):
+        """Summed kernel times since the previous drain: {"blind_rotate": ms, "keyswitch": ms, "calls": n}."""
+        arr = (C.c_double * 2)()
+        calls = C.c_int32()
+        _lib.check(_lib.load().b200_timing_drain(self._h, C.byref(arr), C.byref(calls)))
+        return {"blind_rotate": arr[0], "keyswitch": arr[1], "calls": calls.value}
+
     # ---- gates -----------------------------------------------------------------------------
     def _rowlen(self):
         return self.params.n + 1
@@ -247,6 +264,13 @@ class CloudKey:
         arr = (C.c_float * 3)()
         _lib.check(_lib.load().b200_last_timing_ms(self._h, C.byref(arr)))
         return {"blind_rotate": arr[0], "keyswitch": arr[1], "total": arr[2]}
+
+
+def fp64_peak_tflops(device=0):
+    """FP64 FMA peak of the device measured by the library's DFMA-chain kernel (TFLOP/s)."""
+    v = C.c_double()
+    _lib.check(_lib.load().b200_fp64_peak_tflops(int(device), C.byref(v)))
+    return v.value
 
 
 def launch_count():

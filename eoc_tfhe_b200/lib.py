@@ -45,6 +45,8 @@ SIGNATURES = {
     "b200_expand_gates": (C.c_int, [_VP, C.c_int64, _VP, C.POINTER(C.c_int64), _VP, C.POINTER(C.c_int64)]),
     "b200_level_run_dev": (C.c_int, [_VP, _VP, _VP, C.c_int64, _VP, C.c_int64, _VP]),
     "b200_last_timing_ms": (C.c_int, [_VP, C.POINTER(C.c_float * 3)]),
+    "b200_timing_drain": (C.c_int, [_VP, C.POINTER(C.c_double * 2), C.POINTER(C.c_int32)]),
+    "b200_fp64_peak_tflops": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
     "b200_launch_count": (C.c_int64, []),
     "bootsGate_batch": (C.c_int, [C.c_int, _VP, _VP, _VP, _VP, C.c_int32, _VP]),
 }

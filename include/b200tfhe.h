@@ -265,6 +265,12 @@ int  b200_level_run_dev(b200_key *key, int32_t *d_wires, const int32_t *rot_desc
  * of the most recent *_host / *_dev call on this key: [0]=blind rotation, [1]=key switch,
  * [2]=total incl. copies. Synchronises the stream. */
 int  b200_last_timing_ms(b200_key *key, float out_ms[3]);
+/* Sum of the per-kernel GPU times ([0] blind rotation, [1] key switch, ms) of every gate-batch call
+ * since the previous drain (at most the last 64 calls), and how many calls that was. Synchronises. */
+int  b200_timing_drain(b200_key *key, double sum_ms[2], int32_t *calls);
+/* FP64 FMA throughput of `device` measured by a DFMA-chain kernel (TFLOP/s): the roofline
+ * denominator bench.py reports the blind rotation against. */
+int  b200_fp64_peak_tflops(int device, double *tflops);
 /* Number of kernels this library has launched since load (bench.py's gpu_launches). */
 int64_t b200_launch_count(void);
 
