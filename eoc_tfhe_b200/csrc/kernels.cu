@@ -117,12 +117,91 @@ __host__ __device__ __forceinline__ void gate_coeffs(int op, int half, int &s0, 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Bootstrapping-key row providers for cmux_step.  A "row pair" is the two evaluation-domain
+// polynomials (c = 0, 1) of TGSW row rp = q*l + p of BK_i: 2 x 512 double2 = 16 KiB, contiguous.
+//   GlobalRows : read straight from global memory / L2 (single-step test kernel)
+//   RingRows   : a shared-memory ring of row pairs filled by TMA bulk copies (cp.async.bulk) that all
+//                ciphertext groups of the CTA consume in lockstep, so one L2 read serves the whole CTA
+//                and the L2 latency is hidden behind the previous transforms.
+// ------------------------------------------------------------------------------------------------
+struct GlobalRows {
+    const double2 *bk_i;
+    __device__ __forceinline__ const double2 *acquire(int rp) const { return bk_i + (size_t)rp * 2 * kM; }
+    __device__ __forceinline__ double2 load(const double2 *p) const { return __ldg(p); }
+    __device__ __forceinline__ void release(int) const {}
+};
+
+constexpr int kStageBytes = 2 * kM * 16;  // one row pair
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    const uint32_t a = smem_u32(bar);
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(a), "r"(parity) : "memory");
+    } while (!done);
+}
+// one thread: announce `bytes` on the barrier and start the bulk copy global -> shared that completes it
+__device__ __forceinline__ void tma_load_row_pair(void *dst, const void *src, uint64_t *bar) {
+    const uint32_t b = smem_u32(bar), d = smem_u32(dst);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(kStageBytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(d), "l"(src), "r"(kStageBytes), "r"(b) : "memory");
+}
+
+template <int STAGES>
+struct RingState {                 // lives in shared memory
+    uint64_t full[STAGES];         // TMA completion barriers
+    int done[STAGES];              // warps that finished reading the stage's current contents
+};
+
+template <int STAGES>
+struct RingRows {
+    unsigned char *ring;           // [STAGES][kStageBytes]
+    RingState<STAGES> *st;
+    const double2 *bk;             // key.bkfft
+    int seq0;                      // sequence number of row pair 0 of the current CMux step (= i * kpl)
+    int total;                     // n * kpl
+    int warps;                     // consumer warps per CTA
+    __device__ __forceinline__ const double2 *acquire(int rp) const {
+        const int q = seq0 + rp;
+        mbar_wait(&st->full[q % STAGES], (uint32_t)(q / STAGES) & 1u);
+        return reinterpret_cast<const double2 *>(ring + (size_t)(q % STAGES) * kStageBytes);
+    }
+    __device__ __forceinline__ double2 load(const double2 *p) const { return *p; }
+    // the calling warp has consumed row pair rp; the last warp of the CTA to say so refills the stage
+    __device__ __forceinline__ void release(int rp) const {
+        const int q = seq0 + rp, s = q % STAGES;
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) {
+            __threadfence_block();
+            if (atomicAdd(&st->done[s], 1) == warps - 1) {
+                st->done[s] = 0;
+                if (q + STAGES < total)
+                    tma_load_row_pair(ring + (size_t)s * kStageBytes, bk + (size_t)(q + STAGES) * 2 * kM, &st->full[s]);
+            }
+        }
+    }
+    // a group that does nothing this step (barai == 0, or no ciphertext) still has to hand the stages on
+    __device__ __forceinline__ void skip_step(int kpl) const {
+        for (int rp = 0; rp < kpl; ++rp) { acquire(rp); release(rp); }
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
 // one CMux step on a shared-memory accumulator, executed by one 64-thread group
 //   MODE 0: ACC <- ACC + BK_i (x) ((X^a - 1) ACC)      (lwe-bootstrapping-functions-fft.cpp:67-76)
 //   MODE 1: ACC <- BK_i (x) ACC                         (tgsw-fft-operations.cpp:89-114)
 // ------------------------------------------------------------------------------------------------
-template <int L, int BGBIT, int MODE, class Barrier>
-__device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int a, const double2 *__restrict__ bk_i,
+template <int L, int BGBIT, int MODE, class Barrier, class Rows>
+__device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int a, const Rows &rows,
                                           const int t, const RootSet &w2, const RootSet &w3, const Barrier &bar) {
     constexpr uint32_t BG = 1u << BGBIT, HALF = BG >> 1, MASK = BG - 1;
     uint32_t offset = 0;  // tgsw.cpp:7-29
@@ -162,11 +241,11 @@ __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int
             }
             negacyclic_forward(x, bufs + toggle * kBufElems, t, w2, w3, bar);
             toggle ^= 1;
-            const double2 *row = bk_i + (size_t)(q * L + p) * 2 * kM + t;
+            const double2 *row = rows.acquire(q * L + p) + t;
 #pragma unroll
             for (int r = 0; r < 8; ++r) {
-                const double2 b0 = __ldg(row + r * 64);
-                const double2 b1 = __ldg(row + kM + r * 64);
+                const double2 b0 = rows.load(row + r * 64);
+                const double2 b1 = rows.load(row + kM + r * 64);
                 acc0[r].x = fma(x[r].x, b0.x, acc0[r].x);
                 acc0[r].x = fma(-x[r].y, b0.y, acc0[r].x);
                 acc0[r].y = fma(x[r].x, b0.y, acc0[r].y);
@@ -176,6 +255,7 @@ __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int
                 acc1[r].y = fma(x[r].x, b1.y, acc1[r].y);
                 acc1[r].y = fma(x[r].y, b1.x, acc1[r].y);
             }
+            rows.release(q * L + p);
         }
     }
     constexpr double kScale = 1.0 / kM;
@@ -199,24 +279,44 @@ __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int
     bar();  // accumulator complete before the next step's rotated reads
 }
 
-constexpr int kBrSmemBytes = 2 * kN * 4 + 2 * kBufElems * 16 + 1280;  // ACC + 2 exchange buffers + bara
+// per ciphertext group: ACC + 2 exchange buffers + bara
+constexpr int kGroupSmemBytes = 2 * kN * 4 + 2 * kBufElems * 16 + 1280;
+constexpr int kBrStages = 4;
+constexpr int br_smem_bytes(int groups) { return groups * kGroupSmemBytes + kBrStages * kStageBytes + 128; }
+constexpr int kCmuxTestSmemBytes = kGroupSmemBytes;
 
 #ifndef BR_MAXREG
-#define BR_MAXREG 200
+#define BR_MAXREG 255
 #endif
-template <int L, int BGBIT>
+// G ciphertexts per CTA (64 threads each), walking i = 0..n-1 in lockstep on one TMA-fed ring of
+// bootstrapping-key row pairs.  Groups synchronise among themselves with named barriers only.
+template <int L, int BGBIT, int G>
 __global__ void __maxnreg__(BR_MAXREG) k_blind_rotate(const DeviceKey key, const BlindRotateArgs a) {
-    extern __shared__ __align__(16) unsigned char smem[];
-    int32_t *ACC = reinterpret_cast<int32_t *>(smem);                         // [2][1024]
-    double2 *bufs = reinterpret_cast<double2 *>(smem + 2 * kN * 4);           // [2][576]
-    uint16_t *bara = reinterpret_cast<uint16_t *>(smem + 2 * kN * 4 + 2 * kBufElems * 16);  // [n+1]
+    extern __shared__ __align__(128) unsigned char smem[];
+    constexpr int KPL = 2 * L;
+    unsigned char *ring = smem;                                                       // [stages][16 KiB]
+    RingState<kBrStages> *st = reinterpret_cast<RingState<kBrStages> *>(smem + kBrStages * kStageBytes);
+    const int g = threadIdx.x >> 6, t = threadIdx.x & 63;
+    unsigned char *mine = smem + kBrStages * kStageBytes + 128 + (size_t)g * kGroupSmemBytes;
+    int32_t *ACC = reinterpret_cast<int32_t *>(mine);                                // [2][1024]
+    double2 *bufs = reinterpret_cast<double2 *>(mine + 2 * kN * 4);                  // [2][576]
+    uint16_t *bara = reinterpret_cast<uint16_t *>(mine + 2 * kN * 4 + 2 * kBufElems * 16);  // [n+1]
 
-    const int t = threadIdx.x;
     const int n = key.n, n1 = n + 1;
-    const int64_t item = blockIdx.x;
+    const int64_t item = (int64_t)blockIdx.x * G + g;
+    const bool live = item < a.items;
+    const int total = n * KPL;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kBrStages; ++s) { mbar_init(&st->full[s], 1); st->done[s] = 0; }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        for (int s = 0; s < kBrStages && s < total; ++s)
+            tma_load_row_pair(ring + (size_t)s * kStageBytes, key.bkfft + (size_t)s * 2 * kM, &st->full[s]);
+    }
 
     // ---- gate prologue + modulus switch to 2N (numeric-functions.cpp:59-65)
-    {
+    if (live) {
         const int32_t *r0, *r1;
         int s0, s1;
         int32_t cst;
@@ -240,10 +340,10 @@ __global__ void __maxnreg__(BR_MAXREG) k_blind_rotate(const DeviceKey key, const
             bara[i] = (uint16_t)((x + 0x00100000u) >> 21);
         }
     }
-    __syncthreads();
+    __syncthreads();  // bara visible; barriers initialised
 
     // ---- ACC = (0, X^{2N-barb} * mu*(1+X+...+X^{N-1}))   (lwe-bootstrapping-functions-fft.cpp:146-148)
-    {
+    if (live) {
         const int barb = bara[n];
         const int32_t mu = a.mu;
 #pragma unroll
@@ -254,25 +354,29 @@ __global__ void __maxnreg__(BR_MAXREG) k_blind_rotate(const DeviceKey key, const
         }
     }
     const RootSet w2 = load_rootset(c_tw.p2[t >> 3]), w3 = load_rootset(c_tw.p3[t]);
-    __syncthreads();
+    const NamedBarrier64 bar{1 + g};
+    bar();
 
     // ---- blind rotation (lwe-bootstrapping-functions-fft.cpp:88-112)
-    const size_t bk_stride = (size_t)2 * L * 2 * kM;  // double2 per TGSW sample
+    RingRows<kBrStages> rows{ring, st, key.bkfft, 0, total, 2 * G};
 #pragma unroll 1
     for (int i = 0; i < n; ++i) {
-        const int ai = bara[i];
-        if (ai == 0) continue;
-        cmux_step<L, BGBIT, 0>(ACC, bufs, ai, key.bkfft + (size_t)i * bk_stride, t, w2, w3, CtaBarrier());
+        rows.seq0 = i * KPL;
+        const int ai = live ? bara[i] : 0;
+        if (ai == 0) { rows.skip_step(KPL); continue; }
+        cmux_step<L, BGBIT, 0>(ACC, bufs, ai, rows, t, w2, w3, bar);
     }
 
     // ---- sample extract at index 0 (lwe.cpp:41-60)
-    int32_t *u = a.u + (size_t)item * (kN + 1);
+    if (live) {
+        int32_t *u = a.u + (size_t)item * (kN + 1);
 #pragma unroll
-    for (int rr = 0; rr < 16; ++rr) {
-        const int j = t + 64 * rr;
-        u[j] = (j == 0) ? ACC[0] : -ACC[kN - j];
+        for (int rr = 0; rr < 16; ++rr) {
+            const int j = t + 64 * rr;
+            u[j] = (j == 0) ? ACC[0] : -ACC[kN - j];
+        }
+        if (t == 0) u[kN] = ACC[kN];
     }
-    if (t == 0) u[kN] = ACC[kN];
 }
 
 template <int L, int BGBIT>
@@ -285,11 +389,11 @@ __global__ void __launch_bounds__(64, 6) k_cmux_test(const DeviceKey key, int32_
     for (int j = t; j < 2 * kN; j += 64) ACC[j] = g[j];
     const RootSet w2 = load_rootset(c_tw.p2[t >> 3]), w3 = load_rootset(c_tw.p3[t]);
     __syncthreads();
-    const double2 *bk_i = key.bkfft + (size_t)bk_index * (2 * L * 2 * kM);
+    const GlobalRows rows{key.bkfft + (size_t)bk_index * (2 * L * 2 * kM)};
     if (mode == 0) {
-        if (barai != 0) cmux_step<L, BGBIT, 0>(ACC, bufs, barai, bk_i, t, w2, w3, CtaBarrier());
+        if (barai != 0) cmux_step<L, BGBIT, 0>(ACC, bufs, barai, rows, t, w2, w3, CtaBarrier());
     } else {
-        cmux_step<L, BGBIT, 1>(ACC, bufs, 0, bk_i, t, w2, w3, CtaBarrier());
+        cmux_step<L, BGBIT, 1>(ACC, bufs, 0, rows, t, w2, w3, CtaBarrier());
     }
     __syncthreads();
     for (int j = t; j < 2 * kN; j += 64) g[j] = ACC[j];
@@ -452,17 +556,17 @@ __global__ void k_linear_desc(int32_t *pool, const int32_t *desc, int n1) {
         else return cudaErrorInvalidValue;                                          \
     } while (0)
 
-template <int L, int BGBIT>
+template <int L, int BGBIT, int G>
 static cudaError_t set_br_attr() {
     static bool done[16] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 16 && done[dev]) return cudaSuccess;
-    cudaError_t e = cudaFuncSetAttribute(k_blind_rotate<L, BGBIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBrSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(k_blind_rotate<L, BGBIT, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, br_smem_bytes(G));
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_cmux_test<L, BGBIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBrSmemBytes);
+    e = cudaFuncSetAttribute(k_cmux_test<L, BGBIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCmuxTestSmemBytes);
     if (e != cudaSuccess) return e;
-    cudaFuncSetAttribute(k_blind_rotate<L, BGBIT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    cudaFuncSetAttribute(k_blind_rotate<L, BGBIT, G>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     if (dev < 16) done[dev] = true;
     return cudaSuccess;
 }
@@ -482,15 +586,22 @@ cudaError_t launch_ks_pack(const DeviceKey &key, const int32_t *d_ks_rows, cudaS
     return cudaGetLastError();
 }
 
+// Ciphertexts per CTA: 4 (one CTA per SM, one key read per 4 ciphertexts) once the batch fills the
+// GPU that way, otherwise 1 so that small batches still spread over all SMs.
+template <int L, int BGBIT, int G>
+static cudaError_t br_launch(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
+    cudaError_t e = set_br_attr<L, BGBIT, G>();
+    if (e != cudaSuccess) return e;
+    const unsigned grid = (unsigned)((a.items + G - 1) / G);
+    k_blind_rotate<L, BGBIT, G><<<grid, 64 * G, br_smem_bytes(G), s>>>(key, a);
+    return cudaSuccess;
+}
 cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
     if (a.items <= 0) return cudaSuccess;
     if (a.items > 0x7fffffffLL || key.n + 1 > 640) return cudaErrorInvalidValue;
-#define BR_LAUNCH(L_, B_)                                                                 \
-    do {                                                                                  \
-        cudaError_t e = set_br_attr<L_, B_>();                                            \
-        if (e != cudaSuccess) return e;                                                   \
-        k_blind_rotate<L_, B_><<<(unsigned)a.items, 64, kBrSmemBytes, s>>>(key, a);       \
-    } while (0)
+    const bool wide = a.items >= 148 * 4;
+    cudaError_t e;
+#define BR_LAUNCH(L_, B_) e = wide ? br_launch<L_, B_, 4>(key, a, s) : br_launch<L_, B_, 1>(key, a, s)
     if (key.l == 2 && key.Bgbit == 10) BR_LAUNCH(2, 10);
     else if (key.l == 3 && key.Bgbit == 7) BR_LAUNCH(3, 7);
     else if (key.l == 2 && key.Bgbit == 8) BR_LAUNCH(2, 8);
@@ -498,6 +609,7 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
     else if (key.l == 4 && key.Bgbit == 6) BR_LAUNCH(4, 6);
     else return cudaErrorInvalidValue;
 #undef BR_LAUNCH
+    if (e != cudaSuccess) return e;
     COUNT_LAUNCH();
     return cudaGetLastError();
 }
@@ -507,9 +619,9 @@ cudaError_t launch_cmux_test(const DeviceKey &key, int32_t *d_acc, int bk_index,
     if (count <= 0) return cudaSuccess;
 #define CT_LAUNCH(L_, B_)                                                                 \
     do {                                                                                  \
-        cudaError_t e = set_br_attr<L_, B_>();                                            \
+        cudaError_t e = set_br_attr<L_, B_, 1>();                                         \
         if (e != cudaSuccess) return e;                                                   \
-        k_cmux_test<L_, B_><<<(unsigned)count, 64, kBrSmemBytes, s>>>(key, d_acc, bk_index, barai, mode); \
+        k_cmux_test<L_, B_><<<(unsigned)count, 64, kCmuxTestSmemBytes, s>>>(key, d_acc, bk_index, barai, mode); \
     } while (0)
     if (key.l == 2 && key.Bgbit == 10) CT_LAUNCH(2, 10);
     else if (key.l == 3 && key.Bgbit == 7) CT_LAUNCH(3, 7);
