@@ -63,6 +63,11 @@ extern "C" int b200_set_device(int device) {
     return 0;
 }
 extern "C" int64_t b200_launch_count(void) { return launch_count(); }
+extern "C" int b200_set_blind_rotate_kernel(int variant) {
+    if (variant != 0 && variant != 1) return b200_fail("blind-rotation kernel variant must be 0 or 1");
+    set_blind_rotate_variant(variant);
+    return 0;
+}
 
 static int check_params(const b200_params *p) {
     if (!p) return fail("params is NULL");
@@ -89,9 +94,12 @@ static int key_alloc(const b200_params *p, b200_key **out) {
     d.ks_stride = (p->n + 1 + 3) & ~3;
     d.device = g_device;
     const int kpl = (d.k + 1) * d.l, base = 1 << d.ks_basebit;
-    d.bkfft_bytes = (size_t)d.n * kpl * (d.k + 1) * (d.N / 2) * sizeof(double2);
+    // both evaluation-domain layouts live in one blob (one broadcast replicates the key)
+    const size_t bk_elems = (size_t)d.n * kpl * (d.k + 1) * (d.N / 2);
+    d.bkfft_bytes = 2 * bk_elems * sizeof(double2);
     d.ks_bytes = (size_t)d.N * d.k * d.ks_t * (base - 1) * d.ks_stride * sizeof(int32_t);
     cudaError_t e = cudaMalloc((void **)&d.bkfft, d.bkfft_bytes);
+    if (e == cudaSuccess) d.bkfft16 = d.bkfft + bk_elems;
     if (e == cudaSuccess) e = cudaMalloc((void **)&d.ks, d.ks_bytes);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking);
     for (int i = 0; i < b200_key::kRing * 3 && e == cudaSuccess; ++i) e = cudaEventCreate(&k->ring[i / 3][i % 3]);

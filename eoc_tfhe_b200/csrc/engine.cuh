@@ -23,7 +23,8 @@ struct DeviceKey {
     int n, N, k, l, Bgbit, ks_t, ks_basebit;
     int ks_stride;            // n+1 rounded up to a multiple of 4 (int4 loads)
     double ks_variance;
-    double2 *bkfft;           // [n][kpl][k+1][8][64]  evaluation domain, pass-3 layout
+    double2 *bkfft;           // [n][kpl][k+1][8][64]  evaluation domain, pass-3 layout of the 64-thread transform
+    double2 *bkfft16;         // [n][kpl][k+1][16][32] evaluation domain, [r][lane] layout of the warp transform
     int32_t *ks;              // [N*k][t][base-1][ks_stride]
     size_t bkfft_bytes, ks_bytes;
     int device;
@@ -39,6 +40,8 @@ struct BlindRotateArgs {
     int32_t mu;               // test-vector value (2^29 for gates)
     int32_t *u;               // out: [items][N+1]
     int64_t items;
+    int pair;                 // 1: warps g and g+4 alternate transform / non-transform blocks
+    int stagger;              // clocks between the start of successive warps of a CTA (set by the launcher)
 };
 constexpr int kOpRaw = 100;
 
@@ -66,6 +69,7 @@ cudaError_t launch_linear(const DeviceKey &key, int32_t *d_out, const int32_t *d
 cudaError_t launch_linear_desc(const DeviceKey &key, int32_t *pool, const int32_t *d_desc /*[items][4]: op,out,in,unused*/,
                                int64_t items, cudaStream_t s);
 int64_t launch_count();
+void set_blind_rotate_variant(int v);  // 0: 64 threads per ciphertext, 1: warp per ciphertext (TMEM)
 cudaError_t measure_fp64_peak(double *tflops);
 
 }  // namespace b200

@@ -13,10 +13,12 @@
 //   k_cmux_test      a single CMux step / external product on caller accumulators (parity tests)
 #include "engine.cuh"
 #include "negacyclic_fft.cuh"
+#include "negacyclic_fft16.cuh"
 #include "../../include/b200tfhe.h"
 
 #include <atomic>
 #include <math.h>
+#include <stdlib.h>
 
 namespace b200 {
 
@@ -50,12 +52,29 @@ static RootSet make_rootset(int level, unsigned b) {
     w.D = cos_tan(c + pi / 4);
     return w;
 }
+static RootSet16 make_rootset16(int level, unsigned b) {
+    RootSet16 w;
+    w.A = cos_tan(block_theta(level, b) / 2);
+    w.B = cos_tan(block_theta(level + 1, 2 * b) / 2);
+    w.C = cos_tan(block_theta(level + 2, 4 * b) / 2);
+    w.D = cos_tan(block_theta(level + 2, 4 * b + 2) / 2);
+    w.E = cos_tan(block_theta(level + 3, 8 * b) / 2);
+    w.F = cos_tan(block_theta(level + 3, 8 * b + 2) / 2);
+    w.G = cos_tan(block_theta(level + 3, 8 * b + 4) / 2);
+    w.H = cos_tan(block_theta(level + 3, 8 * b + 6) / 2);
+    return w;
+}
 cudaError_t upload_twiddles() {
     static TwiddleTables h;
     h.p1 = make_rootset(0, 0);
     for (unsigned b = 0; b < 8; ++b) h.p2[b] = make_rootset(3, b);
     for (unsigned b = 0; b < 64; ++b) h.p3[b] = make_rootset(6, b);
-    return cudaMemcpyToSymbol(c_tw, &h, sizeof(h));
+    cudaError_t e = cudaMemcpyToSymbol(c_tw, &h, sizeof(h));
+    if (e != cudaSuccess) return e;
+    static TwiddleTables16 h16;
+    for (unsigned b = 0; b < 2; ++b) h16.p1[b] = make_rootset16(1, b);
+    for (unsigned b = 0; b < 32; ++b) h16.p2[b] = make_rootset16(5, b);
+    return cudaMemcpyToSymbol(c_tw16, &h16, sizeof(h16));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -291,7 +310,7 @@ constexpr int kCmuxTestSmemBytes = kGroupSmemBytes;
 // G ciphertexts per CTA (64 threads each), walking i = 0..n-1 in lockstep on one TMA-fed ring of
 // bootstrapping-key row pairs.  Groups synchronise among themselves with named barriers only.
 template <int L, int BGBIT, int G>
-__global__ void __maxnreg__(BR_MAXREG) k_blind_rotate(const DeviceKey key, const BlindRotateArgs a) {
+__global__ void __maxnreg__(255) k_blind_rotate(const DeviceKey key, const BlindRotateArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr int KPL = 2 * L;
     unsigned char *ring = smem;                                                       // [stages][16 KiB]
@@ -379,9 +398,13 @@ __global__ void __maxnreg__(BR_MAXREG) k_blind_rotate(const DeviceKey key, const
     }
 }
 
+}  // namespace b200
+#include "blind_rotate16.cuh"
+namespace b200 {
+
 template <int L, int BGBIT>
 __global__ void __launch_bounds__(64, 6) k_cmux_test(const DeviceKey key, int32_t *acc, int bk_index, int barai, int mode) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    extern __shared__ __align__(128) unsigned char smem[];
     int32_t *ACC = reinterpret_cast<int32_t *>(smem);
     double2 *bufs = reinterpret_cast<double2 *>(smem + 2 * kN * 4);
     const int t = threadIdx.x;
@@ -409,7 +432,7 @@ constexpr int kKsTile = 8;
 
 template <int T>
 __global__ void __launch_bounds__(160) k_keyswitch(const DeviceKey key, const KeySwitchArgs a, int i_per_split, int nsplit) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    extern __shared__ __align__(128) unsigned char smem[];
     uint16_t *dig = reinterpret_cast<uint16_t *>(smem);  // [kKsTile][i_per_split]
     __shared__ int nz[kKsTile];
     __shared__ int32_t bterm[kKsTile];
@@ -575,6 +598,8 @@ cudaError_t launch_bk_convert(const DeviceKey &key, const int32_t *d_bk_coefs, c
     const int polys = key.n * (key.k + 1) * key.l * (key.k + 1);
     k_bk_convert<<<polys, 64, 0, s>>>(d_bk_coefs, key.bkfft);
     COUNT_LAUNCH();
+    k_bk_convert16<<<polys, 32, 0, s>>>(d_bk_coefs, key.bkfft16);
+    COUNT_LAUNCH();
     return cudaGetLastError();
 }
 
@@ -596,9 +621,74 @@ static cudaError_t br_launch(const DeviceKey &key, const BlindRotateArgs &a, cud
     k_blind_rotate<L, BGBIT, G><<<grid, 64 * G, br_smem_bytes(G), s>>>(key, a);
     return cudaSuccess;
 }
+// Kernel choice: 0 = 64 threads per ciphertext (default), 1 = warp per ciphertext with TMEM accumulators
+// (B200_BR_KERNEL=w16 or b200_set_blind_rotate_kernel(1)).
+static std::atomic<int> g_br_variant{-1};
+void set_blind_rotate_variant(int v) { g_br_variant.store(v); }
+static int br_variant() {
+    int v = g_br_variant.load();
+    if (v < 0) {
+        const char *e = getenv("B200_BR_KERNEL");
+        v = (e && e[0] == 'w') ? 1 : 0;
+        g_br_variant.store(v);
+    }
+    return v;
+}
+template <int L, int BGBIT, int G>
+static cudaError_t br16_launch(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
+    static bool done[16] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!(dev < 16 && done[dev])) {
+        cudaError_t e = cudaFuncSetAttribute(k_blind_rotate16<L, BGBIT, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16_smem_bytes(G));
+        if (e != cudaSuccess) return e;
+        cudaFuncSetAttribute(k_blind_rotate16<L, BGBIT, G>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        if (dev < 16) done[dev] = true;
+    }
+    const unsigned grid = (unsigned)((a.items + G - 1) / G);
+    static int stagger = -1, pad = -1;
+    if (pad < 0) {
+        const char *e = getenv("B200_SMEM_PAD");   // experiments: force one CTA per SM
+        pad = e ? atoi(e) : 0;
+        if (pad) cudaFuncSetAttribute(k_blind_rotate16<L, BGBIT, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    }
+    if (stagger < 0) {
+        const char *e = getenv("B200_STAGGER");
+        stagger = e ? atoi(e) : 0;
+    }
+    static int pair = -1;
+    if (pair < 0) {
+        const char *e = getenv("B200_PAIR");
+        pair = e ? atoi(e) : 0;
+    }
+    BlindRotateArgs a2 = a;
+    a2.stagger = stagger;
+    a2.pair = pair;
+    k_blind_rotate16<L, BGBIT, G><<<grid, 32 * G, pad ? 200 * 1024 : br16_smem_bytes(G), s>>>(key, a2);
+    return cudaSuccess;
+}
 cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
     if (a.items <= 0) return cudaSuccess;
     if (a.items > 0x7fffffffLL || key.n + 1 > 640) return cudaErrorInvalidValue;
+    if (br_variant() == 1) {
+        // 8 ciphertexts per CTA (one CTA per SM, one key read per 8 ciphertexts) once the batch fills
+        // the GPU that way, otherwise one warp per CTA so that small batches spread over all SMs.
+        const bool wide16 = a.items >= 148 * 4;
+        cudaError_t e16;
+        static int gsel = -1;
+        if (gsel < 0) { const char *e = getenv("B200_G"); gsel = e ? atoi(e) : 0; }
+#define BR16_LAUNCH(L_, B_) e16 = gsel == 4 ? br16_launch<L_, B_, 4>(key, a, s) : gsel == 2 ? br16_launch<L_, B_, 2>(key, a, s) : \
+                                  gsel == 1 ? br16_launch<L_, B_, 1>(key, a, s) : wide16 ? br16_launch<L_, B_, 8>(key, a, s) : br16_launch<L_, B_, 1>(key, a, s)
+        if (key.l == 2 && key.Bgbit == 10) BR16_LAUNCH(2, 10);
+        else if (key.l == 3 && key.Bgbit == 7) BR16_LAUNCH(3, 7);
+        else if (key.l == 2 && key.Bgbit == 8) BR16_LAUNCH(2, 8);
+        else if (key.l == 1 && key.Bgbit == 16) BR16_LAUNCH(1, 16);
+        else return cudaErrorInvalidValue;
+#undef BR16_LAUNCH
+        if (e16 != cudaSuccess) return e16;
+        COUNT_LAUNCH();
+        return cudaGetLastError();
+    }
     const bool wide = a.items >= 148 * 4;
     cudaError_t e;
 #define BR_LAUNCH(L_, B_) e = wide ? br_launch<L_, B_, 4>(key, a, s) : br_launch<L_, B_, 1>(key, a, s)
@@ -617,6 +707,23 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
 cudaError_t launch_cmux_test(const DeviceKey &key, int32_t *d_acc, int bk_index, int barai, int mode,
                              int64_t count, cudaStream_t s) {
     if (count <= 0) return cudaSuccess;
+    if (br_variant() == 1) {
+#define CT16_LAUNCH(L_, B_)                                                                                      \
+    do {                                                                                                         \
+        cudaError_t e = cudaFuncSetAttribute(k_cmux_test16<L_, B_>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                             2 * kN * 4 + kBuf16Elems * 16);                                    \
+        if (e != cudaSuccess) return e;                                                                          \
+        k_cmux_test16<L_, B_><<<(unsigned)count, 32, 2 * kN * 4 + kBuf16Elems * 16, s>>>(key, d_acc, bk_index, barai, mode); \
+    } while (0)
+        if (key.l == 2 && key.Bgbit == 10) CT16_LAUNCH(2, 10);
+        else if (key.l == 3 && key.Bgbit == 7) CT16_LAUNCH(3, 7);
+        else if (key.l == 2 && key.Bgbit == 8) CT16_LAUNCH(2, 8);
+        else if (key.l == 1 && key.Bgbit == 16) CT16_LAUNCH(1, 16);
+        else return cudaErrorInvalidValue;
+#undef CT16_LAUNCH
+        COUNT_LAUNCH();
+        return cudaGetLastError();
+    }
 #define CT_LAUNCH(L_, B_)                                                                 \
     do {                                                                                  \
         cudaError_t e = set_br_attr<L_, B_, 1>();                                         \

@@ -182,6 +182,9 @@ __device__ __forceinline__ void negacyclic_inverse(double2 (&x)[8], double2 *buf
 
 // exact int32 -> double for |v| < 2^31 with one integer op and one DADD (no I2F on the slow pipe)
 __device__ __forceinline__ double int_to_double(int32_t v) {
+#ifdef B200_I2F
+    return (double)v;
+#endif
     return __hiloint2double(0x43300000, (int)(0x80000000u ^ (uint32_t)v)) - 4503601774854144.0;  // 2^52 + 2^31
 }
 // round-to-nearest of x*scale to an integer, reduced mod 2^32 (|x*scale| < 2^51)

@@ -273,5 +273,11 @@ def fp64_peak_tflops(device=0):
     return v.value
 
 
+def set_blind_rotate_kernel(variant):
+    """0 / "v2": 64 threads per ciphertext (default); 1 / "w16": warp per ciphertext with TMEM accumulators."""
+    v = {"v2": 0, "w16": 1}.get(variant, variant)
+    _lib.check(_lib.load().b200_set_blind_rotate_kernel(int(v)))
+
+
 def launch_count():
     return int(_lib.load().b200_launch_count())

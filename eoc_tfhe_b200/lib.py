@@ -48,6 +48,7 @@ SIGNATURES = {
     "b200_timing_drain": (C.c_int, [_VP, C.POINTER(C.c_double * 2), C.POINTER(C.c_int32)]),
     "b200_fp64_peak_tflops": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
     "b200_launch_count": (C.c_int64, []),
+    "b200_set_blind_rotate_kernel": (C.c_int, [C.c_int]),
     "bootsGate_batch": (C.c_int, [C.c_int, _VP, _VP, _VP, _VP, C.c_int32, _VP]),
 }
 for _g in ("NAND", "OR", "AND", "XOR", "XNOR", "NOR", "ANDNY", "ANDYN", "ORNY", "ORYN"):

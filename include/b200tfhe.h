@@ -271,6 +271,11 @@ int  b200_timing_drain(b200_key *key, double sum_ms[2], int32_t *calls);
 /* FP64 FMA throughput of `device` measured by a DFMA-chain kernel (TFLOP/s): the roofline
  * denominator bench.py reports the blind rotation against. */
 int  b200_fp64_peak_tflops(int device, double *tflops);
+/* Blind-rotation kernel used by subsequent calls: 0 = 64 threads per ciphertext, accumulators in
+ * registers (default); 1 = one warp per ciphertext, 16-point transforms, accumulators in tensor memory
+ * (tcgen05.ld/st).  Both produce results within the same bounds; the choice is a performance knob that
+ * bench.py and the parity tests exercise.  Also settable with B200_BR_KERNEL=v2|w16 before first use. */
+int  b200_set_blind_rotate_kernel(int variant);
 /* Number of kernels this library has launched since load (bench.py's gpu_launches). */
 int64_t b200_launch_count(void);
 

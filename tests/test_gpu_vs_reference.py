@@ -13,14 +13,20 @@ pytestmark = [pytest.mark.gpu,
               pytest.mark.skipif(not reflib.available(), reason="oracle/_ref not built (needs /root/reference)")]
 
 
-@pytest.fixture(scope="module", params=[80, 128], ids=["P80", "P128"])
+# every parity check runs against both blind-rotation kernels (64 threads per ciphertext / warp per
+# ciphertext with TMEM accumulators)
+@pytest.fixture(scope="module", params=[(80, "v2"), (128, "v2"), (80, "w16"), (128, "w16")],
+                ids=["P80-v2", "P128-v2", "P80-w16", "P128-w16"])
 def keys(request):
-    from eoc_tfhe_b200 import CloudKey
+    from eoc_tfhe_b200 import CloudKey, set_blind_rotate_kernel
+    lam, kernel = request.param
+    set_blind_rotate_kernel(kernel)
     ref = reflib.RefLib()
-    rk = ref.keygen(request.param, seed=42)
+    rk = ref.keygen(lam, seed=42)
     ck = CloudKey.from_libtfhe(rk.cloud_ptr)
     yield rk, ck
     ck.close()
+    set_blind_rotate_kernel("v2")
 
 
 def test_params_roundtrip(keys):

@@ -1,0 +1,26 @@
+#!/bin/bash
+# One GPU-box visit: parity tests, bench line, ncu launch list, one full capture of the hot kernels.
+# usage (under gpurun): bash tools/gpu_round.sh <tag> [skip-tests]
+# Everything lands in gpurun_out/<tag>_*; copy what should be judged into profiles/.
+set -u
+TAG=${1:-run}
+OUT=gpurun_out
+mkdir -p $OUT
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $OUT/${TAG}_smi.txt 2>&1
+nproc > $OUT/${TAG}_nproc.txt; lscpu | grep -E "Model name|^CPU\(s\)" >> $OUT/${TAG}_nproc.txt
+if [ "${2:-}" != "skip-tests" ]; then
+  timeout 1500 python -m pytest tests -m gpu -x -q > $OUT/${TAG}_pytest.log 2>&1
+  echo "pytest exit $?" >> $OUT/${TAG}_pytest.log
+  tail -5 $OUT/${TAG}_pytest.log
+fi
+timeout 900 python bench.py --steps 5 --warmup 3 > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err
+echo "bench exit $?"; cat $OUT/${TAG}_bench.json
+# launch list of a short bench run (shares of the step), then full capture of one wave of each hot kernel
+timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $OUT/${TAG}_plain.log 2>&1 &&
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv \
+    --log-file $OUT/${TAG}_launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $OUT/${TAG}_ncu1.log 2>&1
+timeout 300 python scratch/prof_one.py 2368 > $OUT/${TAG}_prof_plain.log 2>&1 &&
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_blind_rotate|k_keyswitch' -s 2 -c 2 \
+    -f -o $OUT/${TAG}_prof python scratch/prof_one.py 2368 > $OUT/${TAG}_ncu2.log 2>&1
+tail -3 $OUT/${TAG}_ncu2.log
+ls -la $OUT
