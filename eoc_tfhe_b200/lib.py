@@ -9,6 +9,12 @@ class B200Error(RuntimeError):
     pass
 
 
+class b200_wire_cloudkey_info(C.Structure):
+    _fields_ = [("lwe_alpha_min", C.c_double), ("lwe_alpha_max", C.c_double), ("tlwe_alpha_min", C.c_double),
+                ("tlwe_alpha_max", C.c_double), ("bk_variance", C.c_double), ("ks_offset", C.c_size_t),
+                ("ks_bytes", C.c_size_t), ("bk_offset", C.c_size_t), ("bk_bytes", C.c_size_t), ("total_bytes", C.c_size_t)]
+
+
 class b200_params(C.Structure):
     _fields_ = [("n", C.c_int32), ("N", C.c_int32), ("k", C.c_int32), ("l", C.c_int32),
                 ("Bgbit", C.c_int32), ("ks_t", C.c_int32), ("ks_basebit", C.c_int32),
@@ -48,6 +54,15 @@ SIGNATURES = {
     "b200_timing_drain": (C.c_int, [_VP, C.POINTER(C.c_double * 2), C.POINTER(C.c_int32)]),
     "b200_fp64_peak_tflops": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
     "b200_launch_count": (C.c_int64, []),
+    "b200_wire_parse_cloudkey": (C.c_int, [_VP, C.c_size_t, C.POINTER(b200_params), C.POINTER(b200_wire_cloudkey_info)]),
+    "b200_key_from_cloudkey_bytes": (C.c_int, [_VP, C.c_size_t, C.POINTER(_VP)]),
+    "b200_key_from_cloudkey_file": (C.c_int, [C.c_char_p, C.POINTER(_VP)]),
+    "b200_wire_cloudkey_size": (C.c_int64, [C.POINTER(b200_params)]),
+    "b200_wire_write_cloudkey": (C.c_int, [_VP, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(b200_params),
+                                           C.POINTER(b200_wire_cloudkey_info), _VP, _VP]),
+    "b200_wire_sample_bytes": (C.c_int64, [C.c_int32]),
+    "b200_wire_read_samples": (C.c_int, [_VP, C.c_size_t, C.c_int32, C.c_int64, _VP, _VP]),
+    "b200_wire_write_samples": (C.c_int, [_VP, C.c_size_t, C.c_int32, C.c_int64, _VP, _VP]),
     "b200_set_blind_rotate_kernel": (C.c_int, [C.c_int]),
     "bootsGate_batch": (C.c_int, [C.c_int, _VP, _VP, _VP, _VP, C.c_int32, _VP]),
 }

@@ -261,6 +261,34 @@ int  b200_expand_gates(const int32_t *gates, int64_t num_gates, int32_t *rot_des
 int  b200_level_run_dev(b200_key *key, int32_t *d_wires, const int32_t *rot_desc, int64_t n_rot,
                         const int32_t *ks_desc, int64_t n_ks, void *stream);
 
+/* ------------------------------------------------------------------------------------------
+ * libtfhe wire format (host only, no device needed except b200_key_from_cloudkey_*): what
+ * export_tfheGateBootstrappingCloudKeySet_toFile and export_gate_bootstrapping_ciphertext_toFile
+ * write (libs/tfhe/src/libtfhe/tfhe_io.cpp:90-107,757-785,883-905,1031-1035,1099-1103).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_wire_cloudkey_info {
+    double lwe_alpha_min, lwe_alpha_max;     /* LWEPARAMS */
+    double tlwe_alpha_min, tlwe_alpha_max;   /* TLWEPARAMS */
+    double bk_variance;                      /* variance stored with the bootstrapping-key block */
+    size_t ks_offset, ks_bytes;              /* int32 [N*k][t][base][n+1] inside the buffer */
+    size_t bk_offset, bk_bytes;              /* int32 [n][(k+1)l][k+1][N] inside the buffer */
+    size_t total_bytes;                      /* bytes consumed by the whole cloud key */
+} b200_wire_cloudkey_info;
+
+/* Parse the text sections of a serialized cloud key and locate its two binary blocks. */
+int  b200_wire_parse_cloudkey(const void *buf, size_t len, b200_params *p, b200_wire_cloudkey_info *info);
+/* Device key straight from a serialized cloud key (new_tfheGateBootstrappingCloudKeySet_fromFile, tfhe_io.cpp:1127). */
+int  b200_key_from_cloudkey_bytes(const void *buf, size_t len, b200_key **out);
+int  b200_key_from_cloudkey_file(const char *path, b200_key **out);
+/* Serialize a cloud key from raw arrays (the layouts of b200_key_create); `alphas` may be NULL. */
+int64_t b200_wire_cloudkey_size(const b200_params *p);
+int  b200_wire_write_cloudkey(void *buf, size_t cap, size_t *written, const b200_params *p,
+                              const b200_wire_cloudkey_info *alphas, const int32_t *bk_coefs, const int32_t *ks_rows);
+/* LWE sample records (uid 42, a[n], b, double variance) <-> contiguous batch int32 [count][n+1]. */
+int64_t b200_wire_sample_bytes(int32_t n);
+int  b200_wire_read_samples(const void *buf, size_t len, int32_t n, int64_t count, int32_t *cts, double *variances);
+int  b200_wire_write_samples(void *buf, size_t cap, int32_t n, int64_t count, const int32_t *cts, const double *variances);
+
 /* Timing helper: milliseconds of GPU time (cudaEvent, on the key's stream) spent in the kernels
  * of the most recent *_host / *_dev call on this key: [0]=blind rotation, [1]=key switch,
  * [2]=total incl. copies. Synchronises the stream. */

@@ -381,6 +381,40 @@ class RefKeys:
         self.L.delete_TLweSample(dst)
         return out
 
+    def export_samples(self, cts):
+        """Bytes written by export_gate_bootstrapping_ciphertext_toFile (tfhe_io.cpp:1214) for each sample."""
+        import tempfile
+        cts = np.asarray(cts, dtype=np.int32)
+        smp = self._new(len(cts))
+        self._fill(smp, cts)
+        L = self.L
+        L.export_gate_bootstrapping_ciphertext_toFile.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        with tempfile.NamedTemporaryFile(suffix=".ct") as tf:
+            f = self.ref.libc.fopen(tf.name.encode(), b"wb")
+            for i in range(len(cts)):
+                L.export_gate_bootstrapping_ciphertext_toFile(f, C.byref(smp[i]), self.sk.contents.params)
+            self.ref.libc.fclose(f)
+            data = open(tf.name, "rb").read()
+        L.delete_LweSample_array(len(cts), smp)
+        return data
+
+    def import_samples(self, data, count):
+        """What import_gate_bootstrapping_ciphertext_fromFile (tfhe_io.cpp:1220) reads back from `data`."""
+        import tempfile
+        smp = self._new(count)
+        L = self.L
+        L.import_gate_bootstrapping_ciphertext_fromFile.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        with tempfile.NamedTemporaryFile(suffix=".ct") as tf:
+            tf.write(data)
+            tf.flush()
+            f = self.ref.libc.fopen(tf.name.encode(), b"rb")
+            for i in range(count):
+                L.import_gate_bootstrapping_ciphertext_fromFile(f, C.byref(smp[i]), self.sk.contents.params)
+            self.ref.libc.fclose(f)
+        out = self._read(smp, count, self.n)
+        L.delete_LweSample_array(count, smp)
+        return out
+
     def export_secret(self, path):
         f = self.ref.libc.fopen(path.encode(), b"wb")
         self.L.export_tfheGateBootstrappingSecretKeySet_toFile(f, self.sk)
