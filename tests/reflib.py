@@ -301,6 +301,20 @@ class RefKeys:
             self.L.delete_LweSample_array(count, s)
         return out, var
 
+    def gate_mt(self, name, a, b, c=None, threads=None):
+        """gate() with one gate stream per host thread (ctypes releases the GIL; the reference's gate
+        evaluation is re-entrant: per-call scratch, thread_local FFT state)."""
+        import os
+        from concurrent.futures import ThreadPoolExecutor
+        threads = threads or len(os.sched_getaffinity(0))
+        count = a.shape[0]
+        cuts = np.linspace(0, count, threads + 1).astype(int)
+        parts = [(cuts[i], cuts[i + 1]) for i in range(threads) if cuts[i + 1] > cuts[i]]
+        with ThreadPoolExecutor(max_workers=len(parts)) as ex:
+            res = list(ex.map(lambda se: self.gate(name, a[se[0]:se[1]], b[se[0]:se[1]],
+                                                   None if c is None else c[se[0]:se[1]]), parts))
+        return np.concatenate([r[0] for r in res]), np.concatenate([r[1] for r in res])
+
     def bootstrap_woks(self, x, mu=1 << 29):
         count = x.shape[0]
         sx, su = self._new(count), self._new(count, extracted=True)
