@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--gates", type=int, default=GATES_PER_GPU, help="gates per GPU per step (default: the BASELINE config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernel", default=None, choices=["v2", "w16"], help="blind-rotation kernel (default: the library's)")
     return ap.parse_args()
 
 
@@ -199,7 +200,7 @@ def main_b200(args):
     import numpy as np
     import torch
     import torch.distributed as dist
-    from eoc_tfhe_b200 import CloudKey, GateOp, PARAMS_80, launch_count, fp64_peak_tflops
+    from eoc_tfhe_b200 import CloudKey, GateOp, PARAMS_80, launch_count, fp64_peak_tflops, set_blind_rotate_kernel, shard
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -210,6 +211,8 @@ def main_b200(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    if args.kernel:
+        set_blind_rotate_kernel(args.kernel)
     P = PARAMS_80
     count = args.gates
     n1 = P.n + 1
@@ -228,15 +231,8 @@ def main_b200(args):
     key_upload_s = time.perf_counter() - t0
     key_bcast_ms = 0.0
     if world > 1:
-        blobs = ck.device_blob_tensors()
         dist.barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for t in blobs:
-            dist.broadcast(t, src=0)
-        e1.record()
-        torch.cuda.synchronize()
-        key_bcast_ms = e0.elapsed_time(e1)
+        key_bcast_ms = shard.broadcast_key(ck, src=0)     # one NCCL broadcast per resident blob
 
     # ---- inputs: synthetic uniformly random ciphertexts, resident in HBM; 2 x 131 MB per GPU > 126 MB L2
     g = torch.Generator(device=dev)
