@@ -1,0 +1,47 @@
+/* node_api_min.h -- the handful of Node-API (N-API v8) declarations the addon uses, declared here because
+ * node_api.h is not present in the build image.  The names, signatures and enum
+ * values are those of Node's stable C ABI (node_api.h / js_native_api.h); when building against a real
+ * Node installation define B200_HAVE_NODE_API_H and the real header is used instead. */
+#ifndef B200_NODE_API_MIN_H
+#define B200_NODE_API_MIN_H
+#ifdef B200_HAVE_NODE_API_H
+#include <node_api.h>
+#else
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+typedef struct napi_env__ *napi_env;
+typedef struct napi_value__ *napi_value;
+typedef struct napi_callback_info__ *napi_callback_info;
+typedef enum { napi_ok = 0, napi_invalid_arg = 1, napi_generic_failure = 9 } napi_status;
+typedef enum {
+    napi_int8_array, napi_uint8_array, napi_uint8_clamped_array, napi_int16_array, napi_uint16_array,
+    napi_int32_array, napi_uint32_array, napi_float32_array, napi_float64_array
+} napi_typedarray_type;
+typedef napi_value (*napi_callback)(napi_env env, napi_callback_info info);
+typedef void (*napi_finalize)(napi_env env, void *finalize_data, void *finalize_hint);
+#define NAPI_AUTO_LENGTH ((size_t)-1)
+
+napi_status napi_create_function(napi_env env, const char *utf8name, size_t length, napi_callback cb, void *data, napi_value *result);
+napi_status napi_set_named_property(napi_env env, napi_value object, const char *utf8name, napi_value value);
+napi_status napi_get_cb_info(napi_env env, napi_callback_info cbinfo, size_t *argc, napi_value *argv, napi_value *this_arg, void **data);
+napi_status napi_get_typedarray_info(napi_env env, napi_value typedarray, napi_typedarray_type *type, size_t *length, void **data, napi_value *arraybuffer, size_t *byte_offset);
+napi_status napi_get_buffer_info(napi_env env, napi_value value, void **data, size_t *length);
+napi_status napi_create_arraybuffer(napi_env env, size_t byte_length, void **data, napi_value *result);
+napi_status napi_create_typedarray(napi_env env, napi_typedarray_type type, size_t length, napi_value arraybuffer, size_t byte_offset, napi_value *result);
+napi_status napi_create_int32(napi_env env, int32_t value, napi_value *result);
+napi_status napi_create_double(napi_env env, double value, napi_value *result);
+napi_status napi_get_value_int32(napi_env env, napi_value value, int32_t *result);
+napi_status napi_create_external(napi_env env, void *data, napi_finalize finalize_cb, void *finalize_hint, napi_value *result);
+napi_status napi_get_value_external(napi_env env, napi_value value, void **result);
+napi_status napi_create_object(napi_env env, napi_value *result);
+napi_status napi_create_string_utf8(napi_env env, const char *str, size_t length, napi_value *result);
+napi_status napi_throw_error(napi_env env, const char *code, const char *msg);
+napi_status napi_get_undefined(napi_env env, napi_value *result);
+#ifdef __cplusplus
+}
+#endif
+#endif
+#endif
