@@ -64,8 +64,14 @@ extern "C" int b200_set_device(int device) {
 }
 extern "C" int64_t b200_launch_count(void) { return launch_count(); }
 extern "C" int b200_set_blind_rotate_kernel(int variant) {
-    if (variant != 0 && variant != 1) return b200_fail("blind-rotation kernel variant must be 0 or 1");
+    if (variant < 0 || variant > 6) return b200_fail("blind-rotation kernel variant must be 0..6");
     set_blind_rotate_variant(variant);
+    return 0;
+}
+
+extern "C" int b200_set_keyswitch_kernel(int variant) {
+    if (variant < 0 || variant > 2) return b200_fail("key-switch kernel variant must be 0 (auto), 1 (gather) or 2 (streaming)");
+    set_keyswitch_variant(variant);
     return 0;
 }
 

@@ -222,7 +222,7 @@ struct RingRows {
 template <int L, int BGBIT, int MODE, class Barrier, class Rows>
 __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int a, const Rows &rows,
                                           const int t, const RootSet &w2, const RootSet &w3, const Barrier &bar) {
-    constexpr uint32_t BG = 1u << BGBIT, HALF = BG >> 1, MASK = BG - 1;
+    constexpr uint32_t BG = 1u << BGBIT, HALF = BG >> 1;
     uint32_t offset = 0;  // tgsw.cpp:7-29
 #pragma unroll
     for (int p = 0; p < L; ++p) offset += HALF << (32 - (p + 1) * BGBIT);
@@ -254,9 +254,7 @@ __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int
             double2 x[8];
 #pragma unroll
             for (int r = 0; r < 8; ++r) {
-                const int32_t dre = (int32_t)((dv[r] >> shift) & MASK) - (int32_t)HALF;
-                const int32_t dim = (int32_t)((dv[r + 8] >> shift) & MASK) - (int32_t)HALF;
-                x[r] = make_double2(int_to_double(dre), int_to_double(dim));
+                x[r] = make_double2(digit_to_double<BGBIT>(dv[r], shift), digit_to_double<BGBIT>(dv[r + 8], shift));
             }
             negacyclic_forward(x, bufs + toggle * kBufElems, t, w2, w3, bar);
             toggle ^= 1;
@@ -301,7 +299,7 @@ __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int
 // per ciphertext group: ACC + 2 exchange buffers + bara
 constexpr int kGroupSmemBytes = 2 * kN * 4 + 2 * kBufElems * 16 + 1280;
 constexpr int kBrStages = 4;
-constexpr int br_smem_bytes(int groups) { return groups * kGroupSmemBytes + kBrStages * kStageBytes + 128; }
+constexpr int br_smem_bytes(int groups, int stages = kBrStages) { return groups * kGroupSmemBytes + stages * kStageBytes + 128; }
 constexpr int kCmuxTestSmemBytes = kGroupSmemBytes;
 
 #ifndef BR_MAXREG
@@ -309,14 +307,14 @@ constexpr int kCmuxTestSmemBytes = kGroupSmemBytes;
 #endif
 // G ciphertexts per CTA (64 threads each), walking i = 0..n-1 in lockstep on one TMA-fed ring of
 // bootstrapping-key row pairs.  Groups synchronise among themselves with named barriers only.
-template <int L, int BGBIT, int G>
+template <int L, int BGBIT, int G, int STAGES = kBrStages>
 __global__ void __maxnreg__(255) k_blind_rotate(const DeviceKey key, const BlindRotateArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr int KPL = 2 * L;
     unsigned char *ring = smem;                                                       // [stages][16 KiB]
-    RingState<kBrStages> *st = reinterpret_cast<RingState<kBrStages> *>(smem + kBrStages * kStageBytes);
+    RingState<STAGES> *st = reinterpret_cast<RingState<STAGES> *>(smem + STAGES * kStageBytes);
     const int g = threadIdx.x >> 6, t = threadIdx.x & 63;
-    unsigned char *mine = smem + kBrStages * kStageBytes + 128 + (size_t)g * kGroupSmemBytes;
+    unsigned char *mine = smem + STAGES * kStageBytes + 128 + (size_t)g * kGroupSmemBytes;
     int32_t *ACC = reinterpret_cast<int32_t *>(mine);                                // [2][1024]
     double2 *bufs = reinterpret_cast<double2 *>(mine + 2 * kN * 4);                  // [2][576]
     uint16_t *bara = reinterpret_cast<uint16_t *>(mine + 2 * kN * 4 + 2 * kBufElems * 16);  // [n+1]
@@ -327,10 +325,10 @@ __global__ void __maxnreg__(255) k_blind_rotate(const DeviceKey key, const Blind
     const int total = n * KPL;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kBrStages; ++s) { mbar_init(&st->full[s], 1); st->done[s] = 0; }
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&st->full[s], 1); st->done[s] = 0; }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        for (int s = 0; s < kBrStages && s < total; ++s)
+        for (int s = 0; s < STAGES && s < total; ++s)
             tma_load_row_pair(ring + (size_t)s * kStageBytes, key.bkfft + (size_t)s * 2 * kM, &st->full[s]);
     }
 
@@ -377,7 +375,7 @@ __global__ void __maxnreg__(255) k_blind_rotate(const DeviceKey key, const Blind
     bar();
 
     // ---- blind rotation (lwe-bootstrapping-functions-fft.cpp:88-112)
-    RingRows<kBrStages> rows{ring, st, key.bkfft, 0, total, 2 * G};
+    RingRows<STAGES> rows{ring, st, key.bkfft, 0, total, 2 * G};
 #pragma unroll 1
     for (int i = 0; i < n; ++i) {
         rows.seq0 = i * KPL;
@@ -400,6 +398,7 @@ __global__ void __maxnreg__(255) k_blind_rotate(const DeviceKey key, const Blind
 
 }  // namespace b200
 #include "blind_rotate16.cuh"
+#include "blind_rotate3.cuh"
 namespace b200 {
 
 template <int L, int BGBIT>
@@ -532,6 +531,10 @@ __global__ void __launch_bounds__(160) k_keyswitch(const DeviceKey key, const Ke
         atomicAdd(a.nonzero + item0 + threadIdx.x, nz[threadIdx.x]);
 }
 
+}  // namespace b200
+#include "keyswitch_tma.cuh"
+namespace b200 {
+
 // zero the destination rows of a descriptor-driven key switch (needed when splits use atomics)
 __global__ void k_zero_rows(int32_t *out, const KsDesc *desc, int64_t items, int n1) {
     const int64_t item = blockIdx.x;
@@ -613,10 +616,32 @@ cudaError_t launch_ks_pack(const DeviceKey &key, const int32_t *d_ks_rows, cudaS
 
 // Ciphertexts per CTA: 4 (one CTA per SM, one key read per 4 ciphertexts) once the batch fills the
 // GPU that way, otherwise 1 so that small batches still spread over all SMs.
+template <int L, int BGBIT, int G, int STAGES>
+static cudaError_t br_launch_st(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
+    static bool done[16] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!(dev < 16 && done[dev])) {
+        cudaError_t e = cudaFuncSetAttribute(k_blind_rotate<L, BGBIT, G, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, br_smem_bytes(G, STAGES));
+        if (e != cudaSuccess) return e;
+        cudaFuncSetAttribute(k_blind_rotate<L, BGBIT, G, STAGES>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        if (dev < 16) done[dev] = true;
+    }
+    const unsigned grid = (unsigned)((a.items + G - 1) / G);
+    k_blind_rotate<L, BGBIT, G, STAGES><<<grid, 64 * G, br_smem_bytes(G, STAGES), s>>>(key, a);
+    return cudaSuccess;
+}
 template <int L, int BGBIT, int G>
 static cudaError_t br_launch(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
     cudaError_t e = set_br_attr<L, BGBIT, G>();
     if (e != cudaSuccess) return e;
+    if (G == 4) {
+        static int st = -1;
+        if (st < 0) { const char *ev = getenv("B200_STAGES"); st = ev ? atoi(ev) : 0; }
+        if (st == 7) return br_launch_st<L, BGBIT, G, 7>(key, a, s);
+        if (st == 6) return br_launch_st<L, BGBIT, G, 6>(key, a, s);
+        if (st == 2) return br_launch_st<L, BGBIT, G, 2>(key, a, s);
+    }
     const unsigned grid = (unsigned)((a.items + G - 1) / G);
     k_blind_rotate<L, BGBIT, G><<<grid, 64 * G, br_smem_bytes(G), s>>>(key, a);
     return cudaSuccess;
@@ -629,7 +654,7 @@ static int br_variant() {
     int v = g_br_variant.load();
     if (v < 0) {
         const char *e = getenv("B200_BR_KERNEL");
-        v = (e && e[0] == 'w') ? 1 : 0;
+        v = (e && e[0] == 'w') ? 1 : (e && e[0] >= '0' && e[0] <= '9') ? atoi(e) : 0;
         g_br_variant.store(v);
     }
     return v;
@@ -670,6 +695,25 @@ static cudaError_t br16_launch(const DeviceKey &key, const BlindRotateArgs &a, c
 cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
     if (a.items <= 0) return cudaSuccess;
     if (a.items > 0x7fffffffLL || key.n + 1 > 640) return cudaErrorInvalidValue;
+    if (br_variant() >= 2 && a.items >= 148 * 4) {
+        // v3: accumulators in tensor memory; variant = 2: 6 groups x 1 ciphertext, 3: 4 groups x 2 ciphertexts,
+        // 4: 5 x 1, 5: 4 x 1, 6: 3 x 2  (small batches keep the one-group-per-CTA latency path below)
+        const int v = br_variant();
+        cudaError_t e3 = cudaErrorInvalidValue;
+#define BR3_LAUNCH(L_, B_)                                                  \
+        e3 = v == 2 ? br3_launch<L_, B_, 6, 1, 3>(key, a, s)                \
+           : v == 3 ? br3_launch<L_, B_, 4, 2, 4>(key, a, s)                \
+           : v == 4 ? br3_launch<L_, B_, 5, 1, 4>(key, a, s)                \
+           : v == 5 ? br3_launch<L_, B_, 4, 1, 4>(key, a, s)                \
+           :          br3_launch<L_, B_, 3, 2, 4>(key, a, s)
+        if (key.l == 2 && key.Bgbit == 10) BR3_LAUNCH(2, 10);
+        else if (key.l == 3 && key.Bgbit == 7) BR3_LAUNCH(3, 7);
+        else return cudaErrorInvalidValue;
+#undef BR3_LAUNCH
+        if (e3 != cudaSuccess) return e3;
+        COUNT_LAUNCH();
+        return cudaGetLastError();
+    }
     if (br_variant() == 1) {
         // 8 ciphertexts per CTA (one CTA per SM, one key read per 8 ciphertexts) once the batch fills
         // the GPU that way, otherwise one warp per CTA so that small batches spread over all SMs.
@@ -741,10 +785,26 @@ cudaError_t launch_cmux_test(const DeviceKey &key, int32_t *d_acc, int bk_index,
     return cudaGetLastError();
 }
 
+static std::atomic<int> g_ks_variant{-1};
+void set_keyswitch_variant(int v) { g_ks_variant.store(v); }
 cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaStream_t s) {
     if (a.items <= 0) return cudaSuccess;
     if (key.ks_basebit != 2 || key.ks_t != 8) return cudaErrorInvalidValue;  // both reference sets: t=8, base 4
     const int Nin = key.N * key.k;
+    // large batches: table streamed once per 64 (48) samples through a TMA-fed shared-memory ring
+    int ks_sel = g_ks_variant.load();   // 0: by batch size, 1: gather kernel, 2: streaming kernel
+    if (ks_sel < 0) { const char *e = getenv("B200_KS"); ks_sel = e ? atoi(e) : 0; g_ks_variant.store(ks_sel); }
+    const int stride4 = key.ks_stride / 4;
+    if (ks_sel != 1 && Nin % kKs2Chunk == 0 && stride4 <= 192) {
+        const bool small = stride4 <= 128;
+        const int64_t per_cta = small ? 4 * kKs2SG : 3 * kKs2SG;
+        if (ks_sel == 2 || a.items >= 148 * per_cta) {
+            cudaError_t e = small ? ks2_launch<64, 4>(key, a, s) : ks2_launch<96, 3>(key, a, s);
+            if (e != cudaSuccess) return e;
+            COUNT_LAUNCH();
+            return cudaGetLastError();
+        }
+    }
     const int64_t tiles = (a.items + kKsTile - 1) / kKsTile;
     // enough CTAs to fill 148 SMs several times over; small batches split the i range instead
     int nsplit = 1;

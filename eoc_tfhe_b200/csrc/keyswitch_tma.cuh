@@ -1,0 +1,213 @@
+// keyswitch_tma.cuh -- key switch for large batches (included by kernels.cu).
+//
+// lweKeySwitch (libs/tfhe/src/libtfhe/lwe-keyswitch-functions.cpp:114-129,228-238), base 4, t = 8:
+//   out = (0, u.b) - sum_{i<N} sum_{j<8, d_ij != 0} KS[i][j][d_ij],   d_ij = two bits of u.a[i] + 2^15
+// The first kernel (k_keyswitch) gathers table rows with LDG per 8-sample tile: 82 % of its issued
+// instructions were digit decode / row select, and every tile pulled the whole 49.5 MB table through L1
+// (405 GB for 65,536 samples).  This one is organised around the table stream instead:
+//   * a CTA owns NG x 16 samples (64 at the 80-bit set); the table is walked ONCE per CTA in
+//     half-coefficient slabs (12 rows = 24 KiB) that TMA bulk copies (cp.async.bulk) drop into a 4-stage
+//     shared-memory ring completing on mbarriers -- L2 traffic falls 8x and rows are read with LDS.128;
+//   * a thread owns two int4 column groups of 16 samples (128 accumulator registers), so one digit
+//     decode serves 8 integer subtractions;
+//   * digits are warp-uniform: they are packed (16 bits per sample and coefficient) by a pre-pass per
+//     chunk of 64 coefficients and moved to uniform registers with redux.sync, so the 3-way row choice is a
+//     uniform branch, not a select.
+// Integer wrap-around arithmetic only: bit-exact in any summation order.
+#pragma once
+
+namespace b200 {
+
+constexpr int kKs2SG = 16;          // samples per group
+constexpr int kKs2Chunk = 64;       // coefficients per digit chunk
+constexpr int kKs2Stages = 4;
+constexpr int kKs2RowsPerStage = 12;  // half of the 24 rows of one coefficient (j = 0..3 or 4..7, h = 1..3)
+
+template <int NG> struct Ks2State {
+    uint64_t full[kKs2Stages];
+    int done[kKs2Stages];
+    int nz[NG * kKs2SG];
+    int32_t bterm[NG * kKs2SG];
+    int32_t outrow[NG * kKs2SG];
+};
+
+__host__ __device__ constexpr int ks2_state_bytes(int NG) { return ((kKs2Stages * 12 + NG * kKs2SG * 12) + 127) / 128 * 128; }
+__host__ __device__ constexpr int ks2_smem_bytes(int NG, int stride) {
+    return kKs2Stages * kKs2RowsPerStage * stride * 4 + 2 * kKs2Chunk * NG * kKs2SG * 2 + ks2_state_bytes(NG);
+}
+
+__device__ __forceinline__ void ks2_sub(int4 &a, const int4 &v) { a.x -= v.x; a.y -= v.y; a.z -= v.z; a.w -= v.w; }
+
+template <int TG, int NG>
+__global__ void __launch_bounds__(TG * NG, 1) k_keyswitch_tma(const DeviceKey key, const KeySwitchArgs a) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    constexpr int T = 8, S = NG * kKs2SG, WARPS = TG * NG / 32;
+    const int Nin = key.N * key.k, n1 = key.n + 1, stride = key.ks_stride, stride4 = stride >> 2;
+    const int stage_bytes = kKs2RowsPerStage * stride * 4;
+    unsigned char *ring = smem;
+    uint16_t *dig = reinterpret_cast<uint16_t *>(smem + kKs2Stages * stage_bytes);     // [2][chunk][S]
+    Ks2State<NG> *st = reinterpret_cast<Ks2State<NG> *>(smem + kKs2Stages * stage_bytes + 2 * kKs2Chunk * S * 2);
+
+    const int grp = threadIdx.x / TG, t = threadIdx.x - grp * TG;
+    const int64_t item0 = (int64_t)blockIdx.x * S;
+    const uint32_t prec_offset = 1u << (32 - (1 + 2 * T));
+    const int total = Nin * 2;                       // half-coefficient slabs
+    const unsigned char *tab = reinterpret_cast<const unsigned char *>(key.ks);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kKs2Stages; ++s) { mbar_init(&st->full[s], 1); st->done[s] = 0; }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        for (int s = 0; s < kKs2Stages && s < total; ++s) {
+            const uint32_t b = smem_u32(&st->full[s]), d = smem_u32(ring + (size_t)s * stage_bytes);
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(stage_bytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(d), "l"(tab + (size_t)s * stage_bytes), "r"(stage_bytes), "r"(b) : "memory");
+        }
+    }
+    // per-sample constants: b term (lwe-keyswitch-functions.cpp:232) and destination row
+    if (threadIdx.x < S) {
+        const int g = threadIdx.x;
+        st->nz[g] = 0;
+        const int64_t item = item0 + g;
+        int32_t b = 0, orow = -1;
+        if (item < a.items) {
+            int64_t u0, u1 = -1;
+            int32_t add = 0;
+            if (a.desc) { const KsDesc d = a.desc[item]; u0 = d.u0; u1 = d.u1; add = d.add_b; orow = d.out; }
+            else if (a.pair) { u0 = 2 * item; u1 = 2 * item + 1; add = 1 << 29; orow = (int32_t)item; }
+            else { u0 = item; orow = (int32_t)item; }
+            b = a.u[u0 * (Nin + 1) + Nin] + add;
+            if (u1 >= 0) b += a.u[u1 * (Nin + 1) + Nin];
+        }
+        st->bterm[g] = b;
+        st->outrow[g] = orow;
+    }
+
+    // digit pre-pass of one chunk (lwe-keyswitch-functions.cpp:122-125): top 2T bits of a_i + prec_offset
+    auto prepass = [&](int chunk) {
+        uint16_t *dst = dig + (size_t)(chunk & 1) * kKs2Chunk * S;
+        const int i0 = chunk * kKs2Chunk;
+        for (int idx = threadIdx.x; idx < S * kKs2Chunk; idx += TG * NG) {
+            const int g = idx / kKs2Chunk, ii = idx - g * kKs2Chunk;
+            const int64_t item = item0 + g;
+            uint32_t packed = 0;
+            if (item < a.items && i0 + ii < Nin) {
+                int64_t u0, u1 = -1;
+                if (a.desc) { const KsDesc d = a.desc[item]; u0 = d.u0; u1 = d.u1; }
+                else if (a.pair) { u0 = 2 * item; u1 = 2 * item + 1; }
+                else u0 = item;
+                uint32_t v = (uint32_t)a.u[u0 * (Nin + 1) + i0 + ii];
+                if (u1 >= 0) v += (uint32_t)a.u[u1 * (Nin + 1) + i0 + ii];
+                packed = (v + prec_offset) >> (32 - 2 * T);
+                const int c = __popc((packed | (packed >> 1)) & 0x5555u);
+                if (c && a.nonzero) atomicAdd(&st->nz[g], c);
+            }
+            dst[ii * S + g] = (uint16_t)packed;
+        }
+    };
+    prepass(0);
+    __syncthreads();
+
+    int4 acc[kKs2SG][2];
+#pragma unroll
+    for (int g = 0; g < kKs2SG; ++g) acc[g][0] = acc[g][1] = make_int4(0, 0, 0, 0);
+    const bool has1 = t + TG < stride4;      // second column group exists for this thread
+    const bool has0 = t < stride4;
+    const int col0 = has0 ? t : 0, col1 = has1 ? t + TG : col0;
+
+    const int nchunks = (Nin + kKs2Chunk - 1) / kKs2Chunk;
+#pragma unroll 1
+    for (int chunk = 0; chunk < nchunks; ++chunk) {
+        if (chunk + 1 < nchunks) prepass(chunk + 1);   // the other buffer; made visible by the barrier below
+        const uint16_t *dg = dig + (size_t)(chunk & 1) * kKs2Chunk * S + grp * kKs2SG;
+        const int icnt = min(kKs2Chunk, Nin - chunk * kKs2Chunk);
+#pragma unroll 1
+        for (int ii = 0; ii < icnt; ++ii) {
+            // 16 samples x 16 bits, warp uniform; redux.sync moves them to uniform registers
+            const uint4 w0 = *reinterpret_cast<const uint4 *>(dg + ii * S);
+            const uint4 w1 = *reinterpret_cast<const uint4 *>(dg + ii * S + 8);
+            uint32_t w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+            for (int k = 0; k < 8; ++k) w[k] = __reduce_or_sync(0xffffffffu, w[k]);
+#pragma unroll 1
+            for (int jh = 0; jh < 2; ++jh) {
+                const int q = (chunk * kKs2Chunk + ii) * 2 + jh, s = q % kKs2Stages;
+                mbar_wait(&st->full[s], (uint32_t)(q / kKs2Stages) & 1u);
+                const int4 *rows = reinterpret_cast<const int4 *>(ring + (size_t)s * stage_bytes);
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) {
+                    int4 r[3][2];
+#pragma unroll
+                    for (int h = 0; h < 3; ++h) {
+                        r[h][0] = rows[(jj * 3 + h) * stride4 + col0];
+                        r[h][1] = rows[(jj * 3 + h) * stride4 + col1];
+                    }
+                    const int sh = 2 * (T - 1 - (jh * 4 + jj));
+#pragma unroll
+                    for (int g = 0; g < kKs2SG; ++g) {
+                        const uint32_t d = ((w[g >> 1] >> (16 * (g & 1))) >> sh) & 3u;
+                        if (d == 1) { ks2_sub(acc[g][0], r[0][0]); ks2_sub(acc[g][1], r[0][1]); }
+                        else if (d == 2) { ks2_sub(acc[g][0], r[1][0]); ks2_sub(acc[g][1], r[1][1]); }
+                        else if (d == 3) { ks2_sub(acc[g][0], r[2][0]); ks2_sub(acc[g][1], r[2][1]); }
+                    }
+                }
+                // hand the stage back; the last warp of the CTA to do so refills it
+                __syncwarp();
+                if ((threadIdx.x & 31) == 0) {
+                    __threadfence_block();
+                    if (atomicAdd(&st->done[s], 1) == WARPS - 1) {
+                        st->done[s] = 0;
+                        if (q + kKs2Stages < total) {
+                            const uint32_t b = smem_u32(&st->full[s]), d = smem_u32(ring + (size_t)s * stage_bytes);
+                            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(stage_bytes) : "memory");
+                            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                         ::"r"(d), "l"(tab + (size_t)(q + kKs2Stages) * stage_bytes), "r"(stage_bytes), "r"(b) : "memory");
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();   // next chunk's digits visible; this chunk's buffer free for the pre-pass after next
+    }
+
+#pragma unroll
+    for (int g = 0; g < kKs2SG; ++g) {
+        const int orow = st->outrow[grp * kKs2SG + g];
+        if (orow < 0) continue;
+        int32_t *o = a.out + (size_t)orow * n1;
+        const int32_t bt = st->bterm[grp * kKs2SG + g];
+#pragma unroll
+        for (int c2 = 0; c2 < 2; ++c2) {
+            if (!(c2 ? has1 : has0)) continue;
+            const int cbase = (c2 ? t + TG : t) * 4;
+            const int32_t vals[4] = {acc[g][c2].x, acc[g][c2].y, acc[g][c2].z, acc[g][c2].w};
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int col = cbase + c;
+                if (col < n1) o[col] = vals[c] + (col == key.n ? bt : 0);
+            }
+        }
+    }
+    if (a.nonzero && threadIdx.x < S && item0 + threadIdx.x < a.items && st->nz[threadIdx.x])
+        atomicAdd(a.nonzero + item0 + threadIdx.x, st->nz[threadIdx.x]);
+}
+
+template <int TG, int NG>
+static cudaError_t ks2_launch(const DeviceKey &key, const KeySwitchArgs &a, cudaStream_t s) {
+    static bool done[16] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const int smem = ks2_smem_bytes(NG, key.ks_stride);
+    if (smem > 227 * 1024) return cudaErrorInvalidValue;
+    if (!(dev < 16 && done[dev])) {
+        cudaError_t e = cudaFuncSetAttribute(k_keyswitch_tma<TG, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        if (dev < 16) done[dev] = true;
+    }
+    const unsigned grid = (unsigned)((a.items + NG * kKs2SG - 1) / (NG * kKs2SG));
+    k_keyswitch_tma<TG, NG><<<grid, TG * NG, smem, s>>>(key, a);
+    return cudaSuccess;
+}
+
+}  // namespace b200

@@ -187,6 +187,15 @@ __device__ __forceinline__ double int_to_double(int32_t v) {
 #endif
     return __hiloint2double(0x43300000, (int)(0x80000000u ^ (uint32_t)v)) - 4503601774854144.0;  // 2^52 + 2^31
 }
+// gadget digit p of (x + offset) as an exact double, centred: ((v >> shift) & (Bg-1)) - Bg/2
+// (tgsw-functions.cpp:298-348).  The unsigned field goes straight into the mantissa of 2^52 and the
+// centring rides on the same DADD: two integer instructions and one DADD per digit.
+template <int BGBIT>
+__device__ __forceinline__ double digit_to_double(uint32_t v, int shift) {
+    constexpr uint32_t MASK = (1u << BGBIT) - 1;
+    constexpr double kBias = 4503599627370496.0 + (double)(1u << (BGBIT - 1));  // 2^52 + Bg/2
+    return __hiloint2double(0x43300000, (int)((v >> shift) & MASK)) - kBias;
+}
 // round-to-nearest of x*scale to an integer, reduced mod 2^32 (|x*scale| < 2^51)
 __device__ __forceinline__ int32_t round_scaled_to_torus(double x, double scale) {
     return __double2loint(fma(x, scale, 6755399441055744.0));  // 1.5 * 2^52

@@ -275,8 +275,14 @@ def fp64_peak_tflops(device=0):
 
 def set_blind_rotate_kernel(variant):
     """0 / "v2": 64 threads per ciphertext (default); 1 / "w16": warp per ciphertext with TMEM accumulators."""
-    v = {"v2": 0, "w16": 1}.get(variant, variant)
+    v = {"v2": 0, "w16": 1, "v3g6": 2, "v3c2": 3, "v3g5": 4, "v3g4": 5, "v3g3c2": 6}.get(variant, variant)
     _lib.check(_lib.load().b200_set_blind_rotate_kernel(int(v)))
+
+
+def set_keyswitch_kernel(variant):
+    """0 / "auto": by batch size; 1 / "gather": 8-sample tiles; 2 / "stream": table streamed by TMA, 64 samples per CTA."""
+    v = {"auto": 0, "gather": 1, "stream": 2}.get(variant, variant)
+    _lib.check(_lib.load().b200_set_keyswitch_kernel(int(v)))
 
 
 def launch_count():

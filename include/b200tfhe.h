@@ -301,9 +301,14 @@ int  b200_timing_drain(b200_key *key, double sum_ms[2], int32_t *calls);
 int  b200_fp64_peak_tflops(int device, double *tflops);
 /* Blind-rotation kernel used by subsequent calls: 0 = 64 threads per ciphertext, accumulators in
  * registers (default); 1 = one warp per ciphertext, 16-point transforms, accumulators in tensor memory
- * (tcgen05.ld/st).  Both produce results within the same bounds; the choice is a performance knob that
- * bench.py and the parity tests exercise.  Also settable with B200_BR_KERNEL=v2|w16 before first use. */
+ * (tcgen05.ld/st); 2..6 = the 64-thread layout with accumulators in tensor memory (2: 6 groups per SM,
+ * 3: 4 groups of two ciphertexts sharing every key read, 4..6: other group shapes), bit-identical to 0.
+ * All produce results within the same bounds; the choice is a performance knob that bench.py and the
+ * parity tests exercise.  Also settable with B200_BR_KERNEL=v2|w16|<number> before first use. */
 int  b200_set_blind_rotate_kernel(int variant);
+/* Key-switch kernel: 0 = chosen by batch size (default), 1 = gather kernel (8-sample tiles, any batch),
+ * 2 = table-streaming kernel (64 samples per CTA, table rows staged by TMA).  Results are identical. */
+int  b200_set_keyswitch_kernel(int variant);
 /* Number of kernels this library has launched since load (bench.py's gpu_launches). */
 int64_t b200_launch_count(void);
 
