@@ -5,11 +5,12 @@
 // The first kernel (k_keyswitch) gathers table rows with LDG per 8-sample tile: 82 % of its issued
 // instructions were digit decode / row select, and every tile pulled the whole 49.5 MB table through L1
 // (405 GB for 65,536 samples).  This one is organised around the table stream instead:
-//   * a CTA owns NG x 16 samples (64 at the 80-bit set); the table is walked ONCE per CTA in
+//   * a CTA owns NG x SG samples (64 at the 80-bit set); the table is walked ONCE per CTA in
 //     half-coefficient slabs (12 rows = 24 KiB) that TMA bulk copies (cp.async.bulk) drop into a 4-stage
 //     shared-memory ring completing on mbarriers -- L2 traffic falls 8x and rows are read with LDS.128;
-//   * a thread owns two int4 column groups of 16 samples (128 accumulator registers), so one digit
-//     decode serves 8 integer subtractions;
+//   * a thread owns two int4 column groups of SG = 8 samples (64 accumulator registers, 16 warps per SM:
+//     the decode -> compare -> branch chain is latency bound, so warps matter more than tile height),
+//     and one digit decode serves 8 integer subtractions;
 //   * digits are warp-uniform: they are packed (16 bits per sample and coefficient) by a pre-pass per
 //     chunk of 64 coefficients and moved to uniform registers with redux.sync, so the 3-way row choice is a
 //     uniform branch, not a select.
@@ -18,35 +19,36 @@
 
 namespace b200 {
 
-constexpr int kKs2SG = 16;          // samples per group
 constexpr int kKs2Chunk = 64;       // coefficients per digit chunk
 constexpr int kKs2Stages = 4;
 constexpr int kKs2RowsPerStage = 12;  // half of the 24 rows of one coefficient (j = 0..3 or 4..7, h = 1..3)
 
-template <int NG> struct Ks2State {
+template <int S> struct Ks2State {   // S = samples per CTA
     uint64_t full[kKs2Stages];
     int done[kKs2Stages];
-    int nz[NG * kKs2SG];
-    int32_t bterm[NG * kKs2SG];
-    int32_t outrow[NG * kKs2SG];
+    int nz[S];
+    int32_t bterm[S];
+    int32_t outrow[S];
 };
 
-__host__ __device__ constexpr int ks2_state_bytes(int NG) { return ((kKs2Stages * 12 + NG * kKs2SG * 12) + 127) / 128 * 128; }
-__host__ __device__ constexpr int ks2_smem_bytes(int NG, int stride) {
-    return kKs2Stages * kKs2RowsPerStage * stride * 4 + 2 * kKs2Chunk * NG * kKs2SG * 2 + ks2_state_bytes(NG);
+__host__ __device__ constexpr int ks2_state_bytes(int S) { return ((kKs2Stages * 12 + S * 12) + 127) / 128 * 128; }
+__host__ __device__ constexpr int ks2_smem_bytes(int S, int stride) {
+    return kKs2Stages * kKs2RowsPerStage * stride * 4 + 2 * kKs2Chunk * S * 2 + ks2_state_bytes(S);
 }
 
 __device__ __forceinline__ void ks2_sub(int4 &a, const int4 &v) { a.x -= v.x; a.y -= v.y; a.z -= v.z; a.w -= v.w; }
 
-template <int TG, int NG>
+// TG threads per group (each owns NC int4 column groups), NG groups per CTA, SG samples per group
+template <int TG, int NG, int SG, int NC>
 __global__ void __launch_bounds__(TG * NG, 1) k_keyswitch_tma(const DeviceKey key, const KeySwitchArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
-    constexpr int T = 8, S = NG * kKs2SG, WARPS = TG * NG / 32;
+    static_assert(SG == 8 || SG == 16, "8 or 16 samples per group");
+    constexpr int T = 8, S = NG * SG, WARPS = TG * NG / 32;
     const int Nin = key.N * key.k, n1 = key.n + 1, stride = key.ks_stride, stride4 = stride >> 2;
     const int stage_bytes = kKs2RowsPerStage * stride * 4;
     unsigned char *ring = smem;
     uint16_t *dig = reinterpret_cast<uint16_t *>(smem + kKs2Stages * stage_bytes);     // [2][chunk][S]
-    Ks2State<NG> *st = reinterpret_cast<Ks2State<NG> *>(smem + kKs2Stages * stage_bytes + 2 * kKs2Chunk * S * 2);
+    Ks2State<S> *st = reinterpret_cast<Ks2State<S> *>(smem + kKs2Stages * stage_bytes + 2 * kKs2Chunk * S * 2);
 
     const int grp = threadIdx.x / TG, t = threadIdx.x - grp * TG;
     const int64_t item0 = (int64_t)blockIdx.x * S;
@@ -83,6 +85,7 @@ __global__ void __launch_bounds__(TG * NG, 1) k_keyswitch_tma(const DeviceKey ke
         st->bterm[g] = b;
         st->outrow[g] = orow;
     }
+    __syncthreads();   // counters zeroed before the pre-pass adds to them; barriers initialised
 
     // digit pre-pass of one chunk (lwe-keyswitch-functions.cpp:122-125): top 2T bits of a_i + prec_offset
     auto prepass = [&](int chunk) {
@@ -109,27 +112,36 @@ __global__ void __launch_bounds__(TG * NG, 1) k_keyswitch_tma(const DeviceKey ke
     prepass(0);
     __syncthreads();
 
-    int4 acc[kKs2SG][2];
+    int4 acc[SG][NC];
 #pragma unroll
-    for (int g = 0; g < kKs2SG; ++g) acc[g][0] = acc[g][1] = make_int4(0, 0, 0, 0);
-    const bool has1 = t + TG < stride4;      // second column group exists for this thread
-    const bool has0 = t < stride4;
-    const int col0 = has0 ? t : 0, col1 = has1 ? t + TG : col0;
+    for (int g = 0; g < SG; ++g)
+#pragma unroll
+        for (int c = 0; c < NC; ++c) acc[g][c] = make_int4(0, 0, 0, 0);
+    int col[NC];
+    bool has[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) { has[c] = t + TG * c < stride4; col[c] = has[c] ? t + TG * c : 0; }
 
     const int nchunks = (Nin + kKs2Chunk - 1) / kKs2Chunk;
 #pragma unroll 1
     for (int chunk = 0; chunk < nchunks; ++chunk) {
         if (chunk + 1 < nchunks) prepass(chunk + 1);   // the other buffer; made visible by the barrier below
-        const uint16_t *dg = dig + (size_t)(chunk & 1) * kKs2Chunk * S + grp * kKs2SG;
+        const uint16_t *dg = dig + (size_t)(chunk & 1) * kKs2Chunk * S + grp * SG;
         const int icnt = min(kKs2Chunk, Nin - chunk * kKs2Chunk);
 #pragma unroll 1
         for (int ii = 0; ii < icnt; ++ii) {
-            // 16 samples x 16 bits, warp uniform; redux.sync moves them to uniform registers
-            const uint4 w0 = *reinterpret_cast<const uint4 *>(dg + ii * S);
-            const uint4 w1 = *reinterpret_cast<const uint4 *>(dg + ii * S + 8);
-            uint32_t w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+            // SG samples x 16 bits, warp uniform; redux.sync moves them to uniform registers
+            uint32_t w[SG / 2];
+            {
+                const uint4 w0 = *reinterpret_cast<const uint4 *>(dg + ii * S);
+                w[0] = w0.x; w[1] = w0.y; w[2] = w0.z; w[3] = w0.w;
+                if (SG == 16) {
+                    const uint4 w1 = *reinterpret_cast<const uint4 *>(dg + ii * S + 8);
+                    w[SG / 2 - 4] = w1.x; w[SG / 2 - 3] = w1.y; w[SG / 2 - 2] = w1.z; w[SG / 2 - 1] = w1.w;
+                }
+            }
 #pragma unroll
-            for (int k = 0; k < 8; ++k) w[k] = __reduce_or_sync(0xffffffffu, w[k]);
+            for (int k = 0; k < SG / 2; ++k) w[k] = __reduce_or_sync(0xffffffffu, w[k]);
 #pragma unroll 1
             for (int jh = 0; jh < 2; ++jh) {
                 const int q = (chunk * kKs2Chunk + ii) * 2 + jh, s = q % kKs2Stages;
@@ -137,19 +149,18 @@ __global__ void __launch_bounds__(TG * NG, 1) k_keyswitch_tma(const DeviceKey ke
                 const int4 *rows = reinterpret_cast<const int4 *>(ring + (size_t)s * stage_bytes);
 #pragma unroll
                 for (int jj = 0; jj < 4; ++jj) {
-                    int4 r[3][2];
+                    int4 r[3][NC];
 #pragma unroll
-                    for (int h = 0; h < 3; ++h) {
-                        r[h][0] = rows[(jj * 3 + h) * stride4 + col0];
-                        r[h][1] = rows[(jj * 3 + h) * stride4 + col1];
-                    }
+                    for (int h = 0; h < 3; ++h)
+#pragma unroll
+                        for (int c = 0; c < NC; ++c) r[h][c] = rows[(jj * 3 + h) * stride4 + col[c]];
                     const int sh = 2 * (T - 1 - (jh * 4 + jj));
 #pragma unroll
-                    for (int g = 0; g < kKs2SG; ++g) {
+                    for (int g = 0; g < SG; ++g) {
                         const uint32_t d = ((w[g >> 1] >> (16 * (g & 1))) >> sh) & 3u;
-                        if (d == 1) { ks2_sub(acc[g][0], r[0][0]); ks2_sub(acc[g][1], r[0][1]); }
-                        else if (d == 2) { ks2_sub(acc[g][0], r[1][0]); ks2_sub(acc[g][1], r[1][1]); }
-                        else if (d == 3) { ks2_sub(acc[g][0], r[2][0]); ks2_sub(acc[g][1], r[2][1]); }
+                        if (d == 1) { _Pragma("unroll") for (int c = 0; c < NC; ++c) ks2_sub(acc[g][c], r[0][c]); }
+                        else if (d == 2) { _Pragma("unroll") for (int c = 0; c < NC; ++c) ks2_sub(acc[g][c], r[1][c]); }
+                        else if (d == 3) { _Pragma("unroll") for (int c = 0; c < NC; ++c) ks2_sub(acc[g][c], r[2][c]); }
                     }
                 }
                 // hand the stage back; the last warp of the CTA to do so refills it
@@ -172,20 +183,20 @@ __global__ void __launch_bounds__(TG * NG, 1) k_keyswitch_tma(const DeviceKey ke
     }
 
 #pragma unroll
-    for (int g = 0; g < kKs2SG; ++g) {
-        const int orow = st->outrow[grp * kKs2SG + g];
+    for (int g = 0; g < SG; ++g) {
+        const int orow = st->outrow[grp * SG + g];
         if (orow < 0) continue;
         int32_t *o = a.out + (size_t)orow * n1;
-        const int32_t bt = st->bterm[grp * kKs2SG + g];
+        const int32_t bt = st->bterm[grp * SG + g];
 #pragma unroll
-        for (int c2 = 0; c2 < 2; ++c2) {
-            if (!(c2 ? has1 : has0)) continue;
-            const int cbase = (c2 ? t + TG : t) * 4;
+        for (int c2 = 0; c2 < NC; ++c2) {
+            if (!has[c2]) continue;
+            const int cbase = (t + TG * c2) * 4;
             const int32_t vals[4] = {acc[g][c2].x, acc[g][c2].y, acc[g][c2].z, acc[g][c2].w};
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-                const int col = cbase + c;
-                if (col < n1) o[col] = vals[c] + (col == key.n ? bt : 0);
+                const int colx = cbase + c;
+                if (colx < n1) o[colx] = vals[c] + (colx == key.n ? bt : 0);
             }
         }
     }
@@ -193,20 +204,20 @@ __global__ void __launch_bounds__(TG * NG, 1) k_keyswitch_tma(const DeviceKey ke
         atomicAdd(a.nonzero + item0 + threadIdx.x, st->nz[threadIdx.x]);
 }
 
-template <int TG, int NG>
+template <int TG, int NG, int SG, int NC>
 static cudaError_t ks2_launch(const DeviceKey &key, const KeySwitchArgs &a, cudaStream_t s) {
     static bool done[16] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
-    const int smem = ks2_smem_bytes(NG, key.ks_stride);
+    const int smem = ks2_smem_bytes(NG * SG, key.ks_stride);
     if (smem > 227 * 1024) return cudaErrorInvalidValue;
     if (!(dev < 16 && done[dev])) {
-        cudaError_t e = cudaFuncSetAttribute(k_keyswitch_tma<TG, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(k_keyswitch_tma<TG, NG, SG, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
         if (dev < 16) done[dev] = true;
     }
-    const unsigned grid = (unsigned)((a.items + NG * kKs2SG - 1) / (NG * kKs2SG));
-    k_keyswitch_tma<TG, NG><<<grid, TG * NG, smem, s>>>(key, a);
+    const unsigned grid = (unsigned)((a.items + NG * SG - 1) / (NG * SG));
+    k_keyswitch_tma<TG, NG, SG, NC><<<grid, TG * NG, smem, s>>>(key, a);
     return cudaSuccess;
 }
 

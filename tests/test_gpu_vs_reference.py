@@ -48,6 +48,31 @@ def test_keyswitch_bit_exact(keys):
     assert np.allclose(nz * rk.ks_variance(), var, rtol=1e-12, atol=0)
 
 
+def test_keyswitch_streaming_kernel_bit_exact(keys):
+    """The table-streaming kernel (TMA-fed ring, 64/40 samples per CTA) against the reference and against the
+    gather kernel: edge rows, a ragged count that leaves a partly filled CTA, non-zero-digit counts."""
+    from eoc_tfhe_b200 import set_keyswitch_kernel
+    rk, ck = keys
+    rng = np.random.default_rng(5)
+    u = rng.integers(-2**31, 2**31, size=(3 * 64 + 37, rk.N + 1), dtype=np.int64).astype(np.int32)
+    u[0] = 0
+    u[1, :rk.N] = -1
+    u[2, :rk.N] = 0x7FFFFFFF
+    u[3, :rk.N] = 0x00007FFF      # one below the rounding offset: every digit 0
+    try:
+        set_keyswitch_kernel("stream")
+        got, nz = ck.keyswitch(u, with_counts=True)
+        set_keyswitch_kernel("gather")
+        got1, nz1 = ck.keyswitch(u, with_counts=True)
+    finally:
+        set_keyswitch_kernel("auto")
+    assert np.array_equal(got, got1) and np.array_equal(nz, nz1)
+    want, var = rk.keyswitch(u[:40])
+    assert np.array_equal(got[:40], want)
+    assert np.allclose(nz[:40] * rk.ks_variance(), var, rtol=1e-12, atol=0)
+    assert nz[3] == 0 and np.array_equal(got[3, :rk.n], np.zeros(rk.n, dtype=np.int32))
+
+
 def test_keyswitch_large_batch_matches_small(keys):
     rk, ck = keys
     rng = np.random.default_rng(2)

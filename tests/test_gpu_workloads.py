@@ -254,3 +254,37 @@ def test_dropin_symbols_on_libtfhe_samples(p80):
     lib.check(L.bootsGate_batch(2, ptrs, ptrs, nxt, None, 4, cloud))
     assert list(rk.decrypt_bits(rk._read(s, 4, rk.n))) == [1, 0, 0, 1]
     rk.L.delete_LweSample_array(4, s)
+
+
+def test_tensor_memory_blind_rotation_variants_bit_identical(p80):
+    """The blind-rotation variants that keep the spectral accumulators in tensor memory (6 groups per SM;
+    two ciphertexts per group sharing every key read) run the same FMA sequence as the default kernel:
+    the extracted samples must be identical word for word, including a ragged tail and an all-zero input
+    (every bara_i = 0, all steps skipped)."""
+    from eoc_tfhe_b200 import set_blind_rotate_kernel
+    rk, ck = p80
+    rng = np.random.default_rng(77)
+    x = rng.integers(-2**31, 2**31, size=(148 * 4 + 13, rk.n + 1), dtype=np.int64).astype(np.int32)
+    x[7] = 0
+    x[8, :200] = 0
+    try:
+        set_blind_rotate_kernel("v2")
+        want = ck.bootstrap_woks(x)
+        for variant in ("v3g6", "v3c2"):
+            set_blind_rotate_kernel(variant)
+            got = ck.bootstrap_woks(x)
+            assert np.array_equal(got, want), variant
+    finally:
+        set_blind_rotate_kernel("v2")
+    # and the result is the reference's up to FFT rounding: same decrypted bit after key switch on real ciphertexts
+    bits = rng.integers(0, 2, size=64).astype(np.int32)
+    cts = rk.encrypt_bits(bits)
+    set_blind_rotate_kernel("v3c2")
+    try:
+        import torch
+        from eoc_tfhe_b200 import GateOp
+        a = torch.from_numpy(np.tile(cts, (10, 1))).cuda()
+        out = ck.gate(GateOp.NAND, a, a)
+    finally:
+        set_blind_rotate_kernel("v2")
+    assert np.array_equal(rk.decrypt_bits(out.cpu().numpy()), np.tile(1 - bits, 10))
