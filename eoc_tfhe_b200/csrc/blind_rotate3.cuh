@@ -49,7 +49,7 @@ __device__ __forceinline__ void forward3(double2 (&x)[C][8], double2 *bufs, int 
 #pragma unroll
         for (int r = 0; r < 8; ++r) bufs[c * kBufElems + base2 + 9 * r] = x[c][r];
     }
-    bar();
+    __syncwarp();  // octet-local exchange (negacyclic_fft.cuh)
 #pragma unroll
     for (int c = 0; c < C; ++c)
 #pragma unroll
@@ -73,7 +73,7 @@ __device__ __forceinline__ void inverse3(double2 (&x)[C][8], double2 *bufs, int 
 #pragma unroll
         for (int r = 0; r < 8; ++r) bufs[c * kBufElems + 9 * t + r] = x[c][r];
     }
-    bar();
+    __syncwarp();  // octet-local exchange
     const int base2 = pad_idx(64 * (t >> 3) + (t & 7));
 #pragma unroll
     for (int c = 0; c < C; ++c)

@@ -373,6 +373,12 @@ __global__ void __maxnreg__(255) k_blind_rotate(const DeviceKey key, const Blind
     const RootSet w2 = load_rootset(c_tw.p2[t >> 3]), w3 = load_rootset(c_tw.p3[t]);
     const NamedBarrier64 bar{1 + g};
     bar();
+    // Groups that share SM sub-partitions (g and g+2) run the same instruction stream; started together
+    // they collide on the FP64 and shared-memory pipes phase by phase.  Offset the second pair.
+    if (a.stagger > 0 && G > 2 && g >= 2) {
+        const long long until = clock64() + (long long)a.stagger;
+        while (clock64() < until) {}
+    }
 
     // ---- blind rotation (lwe-bootstrapping-functions-fft.cpp:88-112)
     RingRows<STAGES> rows{ring, st, key.bkfft, 0, total, 2 * G};
@@ -399,6 +405,7 @@ __global__ void __maxnreg__(255) k_blind_rotate(const DeviceKey key, const Blind
 }  // namespace b200
 #include "blind_rotate16.cuh"
 #include "blind_rotate3.cuh"
+#include "blind_rotate4.cuh"
 namespace b200 {
 
 template <int L, int BGBIT>
@@ -588,11 +595,8 @@ static cudaError_t set_br_attr() {
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 16 && done[dev]) return cudaSuccess;
-    cudaError_t e = cudaFuncSetAttribute(k_blind_rotate<L, BGBIT, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, br_smem_bytes(G));
+    cudaError_t e = cudaFuncSetAttribute(k_cmux_test<L, BGBIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCmuxTestSmemBytes);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_cmux_test<L, BGBIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCmuxTestSmemBytes);
-    if (e != cudaSuccess) return e;
-    cudaFuncSetAttribute(k_blind_rotate<L, BGBIT, G>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     if (dev < 16) done[dev] = true;
     return cudaSuccess;
 }
@@ -628,23 +632,25 @@ static cudaError_t br_launch_st(const DeviceKey &key, const BlindRotateArgs &a, 
         if (dev < 16) done[dev] = true;
     }
     const unsigned grid = (unsigned)((a.items + G - 1) / G);
-    k_blind_rotate<L, BGBIT, G, STAGES><<<grid, 64 * G, br_smem_bytes(G, STAGES), s>>>(key, a);
+    static int stagger = -1;
+    if (stagger < 0) { const char *e = getenv("B200_STAGGER"); stagger = e ? atoi(e) : 0; }
+    BlindRotateArgs a2 = a;
+    a2.stagger = stagger;
+    k_blind_rotate<L, BGBIT, G, STAGES><<<grid, 64 * G, br_smem_bytes(G, STAGES), s>>>(key, a2);
     return cudaSuccess;
 }
+// Ring depth: 7 stages for the 4-ciphertext CTA (everything that fits in 227 KB; 1.9 % faster than 4),
+// 2 stages for the one-ciphertext CTA of small batches so that three of them fit on an SM.
 template <int L, int BGBIT, int G>
 static cudaError_t br_launch(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
-    cudaError_t e = set_br_attr<L, BGBIT, G>();
-    if (e != cudaSuccess) return e;
+    static int st = -1;
+    if (st < 0) { const char *ev = getenv("B200_STAGES"); st = ev ? atoi(ev) : 0; }
     if (G == 4) {
-        static int st = -1;
-        if (st < 0) { const char *ev = getenv("B200_STAGES"); st = ev ? atoi(ev) : 0; }
-        if (st == 7) return br_launch_st<L, BGBIT, G, 7>(key, a, s);
-        if (st == 6) return br_launch_st<L, BGBIT, G, 6>(key, a, s);
-        if (st == 2) return br_launch_st<L, BGBIT, G, 2>(key, a, s);
+        if (st == 4) return br_launch_st<L, BGBIT, G, 4>(key, a, s);
+        return br_launch_st<L, BGBIT, G, 7>(key, a, s);
     }
-    const unsigned grid = (unsigned)((a.items + G - 1) / G);
-    k_blind_rotate<L, BGBIT, G><<<grid, 64 * G, br_smem_bytes(G), s>>>(key, a);
-    return cudaSuccess;
+    if (st == 4) return br_launch_st<L, BGBIT, G, 4>(key, a, s);
+    return br_launch_st<L, BGBIT, G, 2>(key, a, s);
 }
 // Kernel choice: 0 = 64 threads per ciphertext (default), 1 = warp per ciphertext with TMEM accumulators
 // (B200_BR_KERNEL=w16 or b200_set_blind_rotate_kernel(1)).
@@ -695,7 +701,17 @@ static cudaError_t br16_launch(const DeviceKey &key, const BlindRotateArgs &a, c
 cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
     if (a.items <= 0) return cudaSuccess;
     if (a.items > 0x7fffffffLL || key.n + 1 > 640) return cudaErrorInvalidValue;
-    if (br_variant() >= 2 && a.items >= 148 * 4) {
+    if (br_variant() == 7 && a.items >= 148 * 4) {
+        // v4: v2 with the key delivered through tensor memory (tcgen05.cp), one shared-memory read per CTA
+        cudaError_t e4;
+        if (key.l == 2 && key.Bgbit == 10) e4 = br4_launch<2, 10, 4>(key, a, s);
+        else if (key.l == 3 && key.Bgbit == 7) e4 = br4_launch<3, 7, 4>(key, a, s);
+        else return cudaErrorInvalidValue;
+        if (e4 != cudaSuccess) return e4;
+        COUNT_LAUNCH();
+        return cudaGetLastError();
+    }
+    if (br_variant() >= 2 && br_variant() <= 6 && a.items >= 148 * 4) {
         // v3: accumulators in tensor memory; variant = 2: 6 groups x 1 ciphertext, 3: 4 groups x 2 ciphertexts,
         // 4: 5 x 1, 5: 4 x 1, 6: 3 x 2  (small batches keep the one-group-per-CTA latency path below)
         const int v = br_variant();

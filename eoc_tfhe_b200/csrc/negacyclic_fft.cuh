@@ -13,7 +13,9 @@
 //     All butterflies of a block share one root, the twist by w^j is absorbed, and the 512
 //     evaluations come out in bit-reversed-root order with no reordering pass.
 //   * 64 threads x 8 points, three radix-8 passes (9 levels) held in registers, two exchanges
-//     through a padded shared-memory buffer with 128-bit accesses (conflict free).
+//     through a padded shared-memory buffer with 128-bit accesses (conflict free).  Only the exchange
+//     next to pass 1 crosses the two warps (one group barrier per transform); the other one stays inside
+//     octets of threads and needs a __syncwarp only.
 //   * Butterflies in (cos, tan) form: u +- c*(v + i*t*v) costs 6 DFMA instead of 8 FP64 ops.
 //   * Per-thread roots (4 per pass) live in registers for the whole blind rotation; pass-1 roots
 //     are warp-uniform and come from the constant bank.
@@ -153,7 +155,10 @@ __device__ __forceinline__ void negacyclic_forward(double2 (&x)[8], double2 *buf
     fwd_radix8(x, w2);
 #pragma unroll
     for (int r = 0; r < 8; ++r) buf[base2 + 9 * r] = x[r];
-    bar();
+    // The second exchange is an 8x8 transpose inside each aligned octet of threads (thread t reads what
+    // threads 8(t>>3)+r wrote, all within elements 72(t>>3)..72(t>>3)+71 of the padded buffer), i.e. it
+    // never leaves the warp: a warp-level sync replaces the group barrier.
+    __syncwarp();
 #pragma unroll
     for (int r = 0; r < 8; ++r) x[r] = buf[9 * t + r];
     fwd_radix8(x, w3);
@@ -167,7 +172,7 @@ __device__ __forceinline__ void negacyclic_inverse(double2 (&x)[8], double2 *buf
     inv_radix8(x, w3);
 #pragma unroll
     for (int r = 0; r < 8; ++r) buf[9 * t + r] = x[r];
-    bar();
+    __syncwarp();  // octet-local exchange, see negacyclic_forward
     const int base2 = pad_idx(64 * (t >> 3) + (t & 7));
 #pragma unroll
     for (int r = 0; r < 8; ++r) x[r] = buf[base2 + 9 * r];
