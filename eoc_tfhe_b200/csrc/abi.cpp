@@ -108,6 +108,12 @@ static int key_alloc(const b200_params *p, b200_key **out) {
     if (e == cudaSuccess) d.bkfft16 = d.bkfft + bk_elems;
     if (e == cudaSuccess) e = cudaMalloc((void **)&d.ks, d.ks_bytes);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&k->stream_h2d, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&k->stream_d2h, cudaStreamNonBlocking);
+    for (int i = 0; i < b200_key::kSlices && e == cudaSuccess; ++i) {
+        e = cudaEventCreateWithFlags(&k->ev_up[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&k->ev_done[i], cudaEventDisableTiming);
+    }
     for (int i = 0; i < b200_key::kRing * 3 && e == cudaSuccess; ++i) e = cudaEventCreate(&k->ring[i / 3][i % 3]);
     if (e == cudaSuccess) e = cudaEventCreate(&k->ev_start);
     if (e == cudaSuccess) e = upload_twiddles();
@@ -175,6 +181,12 @@ extern "C" void b200_key_free(b200_key *k) {
             if (e) cudaEventDestroy(e);
     if (k->ev_start) cudaEventDestroy(k->ev_start);
     if (k->stream) cudaStreamDestroy(k->stream);
+    if (k->stream_h2d) cudaStreamDestroy(k->stream_h2d);
+    if (k->stream_d2h) cudaStreamDestroy(k->stream_d2h);
+    for (int i = 0; i < b200_key::kSlices; ++i) {
+        if (k->ev_up[i]) cudaEventDestroy(k->ev_up[i]);
+        if (k->ev_done[i]) cudaEventDestroy(k->ev_done[i]);
+    }
     delete k;
 }
 
@@ -333,10 +345,51 @@ static int gate_batch_host_locked(b200_key *k, int op, int32_t *out, const int32
     const bool need_c = op == B200_MUX;
     if ((need_a && !a) || (need_b && !b) || (need_c && !c) || !out) return fail("NULL batch pointer");
     CK(cudaEventRecord(k->ev_start, s));
+    if (k->out.ensure(bytes)) return 1;
+    // Large bootstrapped batches: slice the batch so that the upload of slice i+1 and the download of slice
+    // i-1 overlap the kernels of slice i (three streams).  A slice is a whole number of blind-rotation waves
+    // (148 SMs x 4 ciphertexts x 4) and of 64-sample key-switch tiles.  Snapshot semantics hold: every input
+    // byte is read from the caller's buffers into the device staging copies, never from `out`.
+    constexpr int64_t kSliceQuantum = 148 * 4 * 4;
+    // (an output that overlaps an input at a different offset would break that, so such calls are not sliced)
+    auto shifted_overlap = [&](const int32_t *in) {
+        if (!in || in == out) return false;
+        const char *i0 = (const char *)in, *o0 = (const char *)out;
+        return i0 < o0 + bytes && o0 < i0 + bytes;
+    };
+    if (!op_is_linear(op) && !nonzero && count >= 4 * kSliceQuantum && !shifted_overlap(a) && !shifted_overlap(b) &&
+        !shifted_overlap(need_c ? c : nullptr)) {
+        const int n1 = d.n + 1;
+        int64_t slice = (count + b200_key::kSlices - 1) / b200_key::kSlices;
+        slice = (slice + kSliceQuantum - 1) / kSliceQuantum * kSliceQuantum;
+        if (k->in0.ensure(bytes) || k->in1.ensure(bytes) || (need_c && k->in2.ensure(bytes))) return 1;
+        CK(cudaEventRecord(k->ev_up[0], s));                 // order after earlier work on the key's stream
+        CK(cudaStreamWaitEvent(k->stream_h2d, k->ev_up[0], 0));
+        CK(cudaStreamWaitEvent(k->stream_d2h, k->ev_up[0], 0));
+        int i = 0;
+        for (int64_t g0 = 0; g0 < count; g0 += slice, ++i) {
+            const int64_t g = std::min(slice, count - g0);
+            const size_t off = (size_t)g0 * n1, sb = (size_t)g * n1 * sizeof(int32_t);
+            CK(cudaMemcpyAsync((int32_t *)k->in0.p + off, a + off, sb, cudaMemcpyHostToDevice, k->stream_h2d));
+            CK(cudaMemcpyAsync((int32_t *)k->in1.p + off, b + off, sb, cudaMemcpyHostToDevice, k->stream_h2d));
+            if (need_c) CK(cudaMemcpyAsync((int32_t *)k->in2.p + off, c + off, sb, cudaMemcpyHostToDevice, k->stream_h2d));
+            CK(cudaEventRecord(k->ev_up[i], k->stream_h2d));
+            CK(cudaStreamWaitEvent(s, k->ev_up[i], 0));
+            if (enqueue_gates(k, op, (int32_t *)k->out.p + off, (const int32_t *)k->in0.p + off, (const int32_t *)k->in1.p + off,
+                              need_c ? (const int32_t *)k->in2.p + off : nullptr, g, nullptr, s, i == 0))
+                return 1;
+            CK(cudaEventRecord(k->ev_done[i], s));
+            CK(cudaStreamWaitEvent(k->stream_d2h, k->ev_done[i], 0));
+            CK(cudaMemcpyAsync(out + off, (int32_t *)k->out.p + off, sb, cudaMemcpyDeviceToHost, k->stream_d2h));
+        }
+        CK(cudaStreamSynchronize(k->stream_d2h));
+        CK(cudaStreamSynchronize(s));
+        k->timing_pending = true;
+        return 0;
+    }
     if (need_a) { if (k->in0.ensure(bytes)) return 1; CK(cudaMemcpyAsync(k->in0.p, a, bytes, cudaMemcpyHostToDevice, s)); }
     if (need_b) { if (k->in1.ensure(bytes)) return 1; CK(cudaMemcpyAsync(k->in1.p, b, bytes, cudaMemcpyHostToDevice, s)); }
     if (need_c) { if (k->in2.ensure(bytes)) return 1; CK(cudaMemcpyAsync(k->in2.p, c, bytes, cudaMemcpyHostToDevice, s)); }
-    if (k->out.ensure(bytes)) return 1;
     int32_t *d_nz = nullptr;
     if (nonzero && !op_is_linear(op)) {
         if (k->nz.ensure((size_t)count * sizeof(int32_t))) return 1;

@@ -62,6 +62,10 @@ struct b200_key {
     b200::DeviceKey dk{};
     bool filled = false;
     cudaStream_t stream = nullptr;      // used by the *_host entries
+    // host batches are pipelined in slices: uploads, kernels and downloads run on three streams
+    static constexpr int kSlices = 4;
+    cudaStream_t stream_h2d = nullptr, stream_d2h = nullptr;
+    cudaEvent_t ev_up[kSlices] = {}, ev_done[kSlices] = {};
     std::mutex mu;                      // one call at a time per key (shared workspace)
     DevBuf u, in0, in1, in2, out, nz, desc_rot, desc_ks, desc_lin, acc;
     PinnedBuf stage_in, stage_out;
