@@ -311,6 +311,19 @@ def main_b200(args):
     e2e_value = world * count * e2e_steps / float(t.item())
     same = bool(torch.equal(ho.to(dev), out))   # host-path and device-path results are identical
 
+    # ---- single-gate latency (second half of BASELINE's metric): one bootsNAND through the host entry
+    lat_ms = None
+    if rank == 0:
+        one_a, one_b, one_o = na[:1].copy(), nb[:1].copy(), no[:1].copy()
+        for _ in range(3):
+            ck.gate(GateOp.NAND, one_a, one_b, out=one_o)
+        samples = []
+        for _ in range(15):
+            t0 = time.perf_counter()
+            ck.gate(GateOp.NAND, one_a, one_b, out=one_o)
+            samples.append((time.perf_counter() - t0) * 1e3)
+        lat_ms = sorted(samples)[len(samples) // 2]
+
     if rank == 0:
         hbm_peak, hbm_src = measured_peaks()
         fp64_peak = fp64_peak_tflops(local)
@@ -327,6 +340,7 @@ def main_b200(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * count * n1 * 4, "d2h_bytes_per_step": count * n1 * 4,
                     "steps": e2e_steps, "api": "b200_gate_batch_host (pinned host buffers)", "matches_device_path": same},
             "gpu_launches": int(launches),
+            "latency": {"single_gate_ms": lat_ms, "api": "b200_gate_batch_host, count = 1 (H2D, two kernels, D2H, synchronous)"},
             "roofline": {"bound": "fp64", "kernel": "k_blind_rotate", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
                          "frac": achieved / fp64_peak if fp64_peak else None, "traffic": ncu_traffic("k_blind_rotate"),
                          "ms_per_launch": br, "share_of_step": br / ms_per_step,
@@ -343,6 +357,9 @@ def main_b200(args):
         if not args.no_cpu_baseline and world == 1:
             cb = cpu_reference(96)   # ~1.2 s wall on every host core: 15-20 core-seconds of libtfhe
             line["cpu_baseline"] = {k: v for k, v in cb.items() if not k.startswith("_")}
+            one = run_ref_bench(1, 16)
+            if one:
+                line["latency"]["cpu_single_gate_ms"] = one["ms_per_gate_per_thread"]
         print(json.dumps(line), flush=True)
     ck.close()
     if world > 1:

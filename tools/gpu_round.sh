@@ -1,5 +1,5 @@
 #!/bin/bash
-# One GPU-box visit: parity tests, bench line, ncu launch list, one full capture of the hot kernels.
+# One GPU-box visit: parity tests, bench line, ncu launch list, full captures of the hot kernels, DRAM traffic.
 # usage (under gpurun): bash tools/gpu_round.sh <tag> [skip-tests]
 # Everything lands in gpurun_out/<tag>_*; copy what should be judged into profiles/.
 set -u
@@ -15,12 +15,18 @@ if [ "${2:-}" != "skip-tests" ]; then
 fi
 timeout 900 python bench.py --steps 5 --warmup 3 > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err
 echo "bench exit $?"; cat $OUT/${TAG}_bench.json
-# launch list of a short bench run (shares of the step), then full capture of one wave of each hot kernel
+timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $OUT/${TAG}_bench_reference.json 2>> $OUT/${TAG}_bench.err
+cat $OUT/${TAG}_bench_reference.json
+# launch list of a short bench run (shares of the step)
 timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $OUT/${TAG}_plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv \
     --log-file $OUT/${TAG}_launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $OUT/${TAG}_ncu1.log 2>&1
-timeout 300 python scratch/prof_one.py 2368 > $OUT/${TAG}_prof_plain.log 2>&1 &&
+# DRAM traffic of the two hot kernels at the bench's own launch size (65,536 gates)
+timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum,launch__grid_size --clock-control none \
+    -k regex:'k_blind_rotate|k_keyswitch' -s 2 -c 2 -f -o $OUT/${TAG}_traffic python bench.py --steps 1 --warmup 1 --no-cpu-baseline > $OUT/${TAG}_ncu3.log 2>&1
+# full capture of one launch of each hot kernel (9472 gates = 16 blind-rotation waves, one key-switch wave)
+timeout 300 python scratch/prof_one.py 9472 > $OUT/${TAG}_prof_plain.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_blind_rotate|k_keyswitch' -s 2 -c 2 \
-    -f -o $OUT/${TAG}_prof python scratch/prof_one.py 2368 > $OUT/${TAG}_ncu2.log 2>&1
+    -f -o $OUT/${TAG}_prof python scratch/prof_one.py 9472 > $OUT/${TAG}_ncu2.log 2>&1
 tail -3 $OUT/${TAG}_ncu2.log
-ls -la $OUT
+ls -la $OUT | tail -20
