@@ -64,7 +64,7 @@ extern "C" int b200_set_device(int device) {
 }
 extern "C" int64_t b200_launch_count(void) { return launch_count(); }
 extern "C" int b200_set_blind_rotate_kernel(int variant) {
-    if (variant < 0 || variant > 7) return b200_fail("blind-rotation kernel variant must be 0..7");
+    if (variant < 0 || variant > 8) return b200_fail("blind-rotation kernel variant must be 0..8");
     set_blind_rotate_variant(variant);
     return 0;
 }

@@ -406,6 +406,7 @@ __global__ void __maxnreg__(255) k_blind_rotate(const DeviceKey key, const Blind
 #include "blind_rotate16.cuh"
 #include "blind_rotate3.cuh"
 #include "blind_rotate4.cuh"
+#include "blind_rotate5.cuh"
 namespace b200 {
 
 template <int L, int BGBIT>
@@ -701,6 +702,16 @@ static cudaError_t br16_launch(const DeviceKey &key, const BlindRotateArgs &a, c
 cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
     if (a.items <= 0) return cudaSuccess;
     if (a.items > 0x7fffffffLL || key.n + 1 > 640) return cudaErrorInvalidValue;
+    if (br_variant() == 8 && a.items >= 148 * 4 && key.l == 2 && (key.Bgbit == 10 || key.Bgbit == 8)) {
+        // v5: two warps per ciphertext, each a 16-point-per-thread transform engine owning one polynomial
+        // (small batches stay on v2: a lone v5 ciphertext takes 5.6 us per step against 4.3 us)
+        cudaError_t e5;
+        if (key.Bgbit == 10) e5 = br5_launch<10, 4>(key, a, s);
+        else e5 = br5_launch<8, 4>(key, a, s);
+        if (e5 != cudaSuccess) return e5;
+        COUNT_LAUNCH();
+        return cudaGetLastError();
+    }
     if (br_variant() == 7 && a.items >= 148 * 4) {
         // v4: v2 with the key delivered through tensor memory (tcgen05.cp), one shared-memory read per CTA
         cudaError_t e4;

@@ -16,6 +16,15 @@ a = torch.randint(-2**31, 2**31 - 1, (count, P.n + 1), dtype=torch.int32, device
 b = torch.randint(-2**31, 2**31 - 1, (count, P.n + 1), dtype=torch.int32, device="cuda")
 a[5] = 0; b[5] = 0          # a ciphertext whose bara_i are all zero (every step skipped)
 a[6, :100] = 0; b[6, :100] = 0
+# extracted samples (before key switch) on a small batch: exact difference between kernels
+xs = rng.integers(-2**31, 2**31, size=(148 * 4 + 5, P.n + 1), dtype=np.int64).astype(np.int32)
+uref = None
+for v in variants:
+    set_blind_rotate_kernel(v)
+    u = ck.bootstrap_woks(xs)
+    if uref is None: uref = u
+    d = (u.astype(np.int64) - uref.astype(np.int64) + 2**31) % 2**32 - 2**31
+    print("variant %d: woks max |u - u_first| = %d LSB, rms %.2f" % (v, int(np.abs(d).max()), float(np.sqrt((d.astype(np.float64)**2).mean()))), flush=True)
 ref = None
 for v in variants:
     set_blind_rotate_kernel(v)

@@ -3,7 +3,8 @@ usage: python scratch/small_batches.py"""
 import sys, os, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
-from eoc_tfhe_b200 import CloudKey, PARAMS_80, GateOp
+from eoc_tfhe_b200 import CloudKey, PARAMS_80, GateOp, set_blind_rotate_kernel
+if len(sys.argv) > 1: set_blind_rotate_kernel(int(sys.argv[1]))
 P = PARAMS_80
 rng = np.random.default_rng(0)
 bk = rng.integers(-2**31, 2**31, size=P.bk_shape, dtype=np.int64).astype(np.int32)

@@ -257,10 +257,12 @@ def test_dropin_symbols_on_libtfhe_samples(p80):
 
 
 def test_tensor_memory_blind_rotation_variants_bit_identical(p80):
-    """The blind-rotation variants that keep the spectral accumulators in tensor memory (6 groups per SM;
-    two ciphertexts per group sharing every key read) run the same FMA sequence as the default kernel:
-    the extracted samples must be identical word for word, including a ragged tail and an all-zero input
-    (every bara_i = 0, all steps skipped)."""
+    """The experimental blind-rotation kernels (accumulators in tensor memory: 6 groups per SM / two ciphertexts
+    per group sharing every key read; key delivered through tensor memory by tcgen05.cp; two warps per
+    ciphertext with 16-point transforms) against the default kernel.  Every external product here is an exact
+    integer convolution that the FP64 transforms resolve with a rounding margin far below 1/2, so any correct
+    kernel, whatever its summation order, must produce the SAME extracted samples word for word -- including
+    a ragged tail and an all-zero input (every bara_i = 0, all steps skipped)."""
     from eoc_tfhe_b200 import set_blind_rotate_kernel
     rk, ck = p80
     rng = np.random.default_rng(77)
@@ -270,7 +272,7 @@ def test_tensor_memory_blind_rotation_variants_bit_identical(p80):
     try:
         set_blind_rotate_kernel("v2")
         want = ck.bootstrap_woks(x)
-        for variant in ("v3g6", "v3c2"):
+        for variant in ("v3g6", "v3c2", "v4", "v5"):
             set_blind_rotate_kernel(variant)
             got = ck.bootstrap_woks(x)
             assert np.array_equal(got, want), variant
