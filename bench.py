@@ -220,6 +220,8 @@ def main_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # stdout carries exactly one JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION/INFO) off it
+        os.environ["NCCL_DEBUG"] = os.environ.get("B200_NCCL_DEBUG", "WARN")
         dist.init_process_group("nccl", device_id=dev)
     if args.kernel:
         set_blind_rotate_kernel(args.kernel)
