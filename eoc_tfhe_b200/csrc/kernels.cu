@@ -824,11 +824,14 @@ cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaS
     const int stride4 = key.ks_stride / 4;
     if (ks_sel != 1 && Nin % kKs2Chunk == 0 && stride4 <= 192) {
         const bool small = stride4 <= 128;
+        // 16 warps per SM, 8 samples x 2 int4 column groups per thread (measured best of the shapes tried:
+        // 16 samples per group -> 8 warps, 43 ms; digit pairs with a 16-way branch -> 34-49 ms; this -> 26 ms).
+        // Batches that cannot fill 148 CTAs of 64 samples use CTAs of 32 (two per SM) down to 2,960 samples (below that the gather kernel is as fast).
         const int64_t per_cta = small ? 64 : 40;
-        if (ks_sel == 2 || a.items >= 148 * per_cta) {
-            // 16 warps per SM, 8 samples x 2 int4 column groups per thread (measured best of the shapes tried:
-            // 16 samples per group -> 8 warps, 43 ms; digit pairs with a 16-way branch -> 34-49 ms; this -> 26 ms)
-            cudaError_t e = small ? ks2_launch<64, 8, 8, 2>(key, a, s) : ks2_launch<96, 5, 8, 2>(key, a, s);
+        const bool full = a.items >= 148 * per_cta;
+        if (ks_sel == 2 || a.items >= 148 * 20) {
+            cudaError_t e = small ? (full ? ks2_launch<64, 8, 8, 2>(key, a, s) : ks2_launch<64, 4, 8, 2>(key, a, s))
+                                  : (full ? ks2_launch<96, 5, 8, 2>(key, a, s) : ks2_launch<96, 3, 8, 2>(key, a, s));
             if (e != cudaSuccess) return e;
             COUNT_LAUNCH();
             return cudaGetLastError();

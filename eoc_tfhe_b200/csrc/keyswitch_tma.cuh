@@ -40,7 +40,7 @@ __device__ __forceinline__ void ks2_sub(int4 &a, const int4 &v) { a.x -= v.x; a.
 
 // TG threads per group (each owns NC int4 column groups), NG groups per CTA, SG samples per group
 template <int TG, int NG, int SG, int NC>
-__global__ void __launch_bounds__(TG * NG, 1) k_keyswitch_tma(const DeviceKey key, const KeySwitchArgs a) {
+__global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keyswitch_tma(const DeviceKey key, const KeySwitchArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     static_assert(SG == 8 || SG == 16, "8 or 16 samples per group");
     constexpr int T = 8, S = NG * SG, WARPS = TG * NG / 32;

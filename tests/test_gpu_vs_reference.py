@@ -71,6 +71,16 @@ def test_keyswitch_streaming_kernel_bit_exact(keys):
     assert np.array_equal(got[:40], want)
     assert np.allclose(nz[:40] * rk.ks_variance(), var, rtol=1e-12, atol=0)
     assert nz[3] == 0 and np.array_equal(got[3, :rk.n], np.zeros(rk.n, dtype=np.int32))
+    # a batch large enough for the 64-sample CTAs (the call above ran the 32-sample shape), ragged again
+    big = rng.integers(-2**31, 2**31, size=(148 * 64 + 21, rk.N + 1), dtype=np.int64).astype(np.int32)
+    try:
+        set_keyswitch_kernel("stream")
+        g2, n2 = ck.keyswitch(big, with_counts=True)
+        set_keyswitch_kernel("gather")
+        g1, n1 = ck.keyswitch(big, with_counts=True)
+    finally:
+        set_keyswitch_kernel("auto")
+    assert np.array_equal(g1, g2) and np.array_equal(n1, n2)
 
 
 def test_keyswitch_large_batch_matches_small(keys):
