@@ -290,3 +290,38 @@ def test_tensor_memory_blind_rotation_variants_bit_identical(p80):
     finally:
         set_blind_rotate_kernel("v2")
     assert np.array_equal(rk.decrypt_bits(out.cpu().numpy()), np.tile(1 - bits, 10))
+
+
+def test_random_gate_stream_with_dependencies(p80):
+    """The reference's long-run stress (test-long-run.cpp:61-185: a stream of random gates of every type whose
+    operands are earlier results) as a netlist: 3,000 random gates over 32 encrypted inputs, all fifteen gate
+    kinds including NOT / COPY / CONSTANT and in-place style reuse of recent outputs, 24 independent instances,
+    scheduled by the levelizer (dependency tracking) and checked bit for bit against the plaintext model."""
+    from eoc_tfhe_b200 import circuits, GateOp
+    rk, ck = p80
+    rng = np.random.default_rng(4242)
+    nl = circuits.Netlist()
+    ins = nl.input("x", 32)
+    live = list(ins)
+    ops = [GateOp.NAND, GateOp.OR, GateOp.AND, GateOp.XOR, GateOp.XNOR, GateOp.NOR, GateOp.ANDNY, GateOp.ANDYN,
+           GateOp.ORNY, GateOp.ORYN, GateOp.MUX, GateOp.NOT, GateOp.COPY, GateOp.CONST0, GateOp.CONST1]
+    for _ in range(3000):
+        op = ops[int(rng.integers(0, len(ops)))]
+        # operands: mostly recent results (deep dependency chains), sometimes anything earlier
+        def pick():
+            return live[-int(rng.integers(1, 9))] if rng.random() < 0.7 else live[int(rng.integers(0, len(live)))]
+        if op == GateOp.MUX: w = nl.gate(op, pick(), pick(), pick())
+        elif op in (GateOp.NOT, GateOp.COPY): w = nl.gate(op, pick())
+        elif op in (GateOp.CONST0, GateOp.CONST1): w = nl.gate(op)
+        else: w = nl.gate(op, pick(), pick())
+        live.append(w)
+    nl.outputs["y"] = live[-256:]
+    count = 24
+    bits = rng.integers(0, 2, size=(count, 32)).astype(np.int32)
+    cx = rk.encrypt_bits(bits.ravel()).reshape(count, 32, -1)
+    outs, levels = circuits.run_batch(ck, nl, {"x": cx}, count)
+    assert levels == nl.levelize()[1] and levels > 50          # long dependency chains
+    got = rk.decrypt_bits(outs["y"].reshape(count * 256, -1)).reshape(count, 256)
+    plain = nl.evaluate_plain({w: bits[:, i] for i, w in enumerate(ins)})
+    want = np.stack([np.broadcast_to(np.asarray(plain[w]), (count,)) for w in nl.outputs["y"]], axis=1)
+    assert np.array_equal(got, want)
