@@ -407,6 +407,7 @@ __global__ void __maxnreg__(255) k_blind_rotate(const DeviceKey key, const Blind
 #include "blind_rotate3.cuh"
 #include "blind_rotate4.cuh"
 #include "blind_rotate5.cuh"
+#include "blind_rotate_lat.cuh"
 namespace b200 {
 
 template <int L, int BGBIT>
@@ -702,6 +703,19 @@ static cudaError_t br16_launch(const DeviceKey &key, const BlindRotateArgs &a, c
 cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
     if (a.items <= 0) return cudaSuccess;
     if (a.items > 0x7fffffffLL || key.n + 1 > 640) return cudaErrorInvalidValue;
+    {
+        // at most one ciphertext per SM: the latency kernel spreads each CMux step over 2l groups
+        static int lat = -1;
+        if (lat < 0) { const char *e = getenv("B200_LAT"); lat = e ? atoi(e) : 1; }
+        if (lat && a.items <= 148 && br_variant() == 0) {
+            cudaError_t el = cudaErrorInvalidValue;
+            if (key.l == 2 && key.Bgbit == 10) el = lat_launch<2, 10>(key, a, s);
+            else if (key.l == 3 && key.Bgbit == 7) el = lat_launch<3, 7>(key, a, s);
+            else if (key.l == 2 && key.Bgbit == 8) el = lat_launch<2, 8>(key, a, s);
+            if (el == cudaSuccess) { COUNT_LAUNCH(); return cudaGetLastError(); }
+            if (el != cudaErrorInvalidValue) return el;
+        }
+    }
     if (br_variant() == 8 && a.items >= 148 * 4 && key.l == 2 && (key.Bgbit == 10 || key.Bgbit == 8)) {
         // v5: two warps per ciphertext, each a 16-point-per-thread transform engine owning one polynomial
         // (small batches stay on v2: a lone v5 ciphertext takes 5.6 us per step against 4.3 us)

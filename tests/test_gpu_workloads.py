@@ -276,6 +276,12 @@ def test_tensor_memory_blind_rotation_variants_bit_identical(p80):
             set_blind_rotate_kernel(variant)
             got = ck.bootstrap_woks(x)
             assert np.array_equal(got, want), variant
+        # the latency kernel (at most 148 rotations per launch: one ciphertext per CTA, 2l groups per step)
+        # and the one-group-per-CTA path (149..591) against the same samples
+        set_blind_rotate_kernel("v2")
+        assert np.array_equal(ck.bootstrap_woks(x[:100]), want[:100])
+        assert np.array_equal(ck.bootstrap_woks(x[:1]), want[:1])
+        assert np.array_equal(ck.bootstrap_woks(x[:300]), want[:300])
     finally:
         set_blind_rotate_kernel("v2")
     # and the result is the reference's up to FFT rounding: same decrypted bit after key switch on real ciphertexts
