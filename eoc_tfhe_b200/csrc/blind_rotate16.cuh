@@ -50,15 +50,6 @@ __device__ __forceinline__ void tmem_ld4(uint32_t addr, double2 (&v)[4]) {
     for (int k = 0; k < 4; ++k) tmem_ld1(addr + 4 * k, v[k]);
 }
 
-// Two warps that share an SM sub-partition (warps g and g+4) hand the FP64 pipe back and forth: every
-// CMux step is cut into transform blocks (FP64 bound) and the blocks between them (operand load,
-// spectral MAC, rounding: issue / shared-memory bound); the partner runs one block behind, so that one
-// warp's transforms overlap the other's integer and memory work instead of colliding with its transforms.
-__device__ __forceinline__ void pair_sync(const int id) {
-    if (id) asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory");
-}
-template <int L> __host__ __device__ constexpr int pair_syncs_per_step() { return 2 * (2 * L + 2); }
-
 // TMEM columns of one warp
 constexpr int kTmAcc0 = 0, kTmAcc1 = 64, kTmStash = 128, kTmColsPerWarp = 256;
 
@@ -77,8 +68,7 @@ struct GlobalRows16 {
 // ------------------------------------------------------------------------------------------------
 template <int L, int BGBIT, int MODE, class Rows>
 __device__ __forceinline__ void cmux_step16(int32_t *ACC, double2 *buf, const int a, const Rows &rows, const int lane,
-                                            const RootSet16 &w1, const RootSet16 &w2, const uint32_t tm,
-                                            const int pair = 0) {
+                                            const RootSet16 &w1, const RootSet16 &w2, const uint32_t tm) {
     constexpr uint32_t BG = 1u << BGBIT, HALF = BG >> 1, MASK = BG - 1;
     uint32_t offset = 0;  // tgsw.cpp:7-29
 #pragma unroll
@@ -135,9 +125,7 @@ __device__ __forceinline__ void cmux_step16(int32_t *ACC, double2 *buf, const in
                 for (int r4 = 0; r4 < 4; ++r4) tmem_ld4(tm + kTmStash + 64 * (p - 1) + 16 * r4, *reinterpret_cast<double2(*)[4]>(&x[4 * r4]));
                 tmem_wait_ld();
             }
-            pair_sync(pair);
             forward16_tail(x, buf, lane, w1, w2);
-            pair_sync(pair);
             const double2 *row = rows.acquire(q * L + p) + lane;
             const bool first = (q == 0 && p == 0);
             tmem_wait_st();  // the previous row's accumulator stores have landed
@@ -184,9 +172,7 @@ __device__ __forceinline__ void cmux_step16(int32_t *ACC, double2 *buf, const in
 #pragma unroll
         for (int r4 = 0; r4 < 4; ++r4) tmem_ld4(tm + (c ? kTmAcc1 : kTmAcc0) + 16 * r4, *reinterpret_cast<double2(*)[4]>(&x[4 * r4]));
         tmem_wait_ld();
-        pair_sync(pair);
         inverse16_head(x, buf, lane, w1, w2);
-        pair_sync(pair);
         int32_t *P = ACC + c * kN;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -285,15 +271,6 @@ __global__ void __launch_bounds__(32 * G, 1) k_blind_rotate16(const DeviceKey ke
     }
     const RootSet16 w1 = load_rootset16(c_tw16.p1[lane >> 4]), w2 = load_rootset16(c_tw16.p2[lane]);
     __syncwarp();
-    // The warps of a CTA run the same instruction stream; started together they stay in phase and take
-    // turns saturating the FP64 pipes and the shared-memory pipe.  Start them a fraction of a CMux step
-    // apart so that one warp's transforms overlap another's exchanges and operand loads.
-    if (a.stagger > 0 && G > 1) {
-        const long long until = clock64() + (long long)a.stagger * (((g & 3) << 1) | (g >> 2));
-        while (clock64() < until) {}
-    }
-    const int pair = (G == 8 && a.pair) ? 1 + (g & 3) : 0;
-    if (pair && g >= 4) pair_sync(pair);  // the second warp of a pair runs one block behind
 
     // ---- blind rotation (lwe-bootstrapping-functions-fft.cpp:88-112)
     RingRows<kBr16Stages> rows{ring, st, key.bkfft16, 0, total, G};
@@ -303,12 +280,10 @@ __global__ void __launch_bounds__(32 * G, 1) k_blind_rotate16(const DeviceKey ke
         const int ai = live ? bara[i] : 0;
         if (ai == 0) {
             rows.skip_step(KPL);
-            for (int k = 0; k < pair_syncs_per_step<L>(); ++k) pair_sync(pair);
             continue;
         }
-        cmux_step16<L, BGBIT, 0>(ACC, buf, ai, rows, lane, w1, w2, tm, pair);
+        cmux_step16<L, BGBIT, 0>(ACC, buf, ai, rows, lane, w1, w2, tm);
     }
-    if (pair && g < 4) pair_sync(pair);
 
     // ---- sample extract at index 0 (lwe.cpp:41-60)
     if (live) {

@@ -208,7 +208,7 @@ template <int G> __host__ __device__ constexpr int br4_smem_bytes() { return kV4
 
 template <int L, int BGBIT, int G>
 __global__ void __maxnreg__(255) k_blind_rotate4(const DeviceKey key, const BlindRotateArgs a) {
-    extern __shared__ __align__(1024) unsigned char smem[];
+    extern __shared__ __align__(128) unsigned char smem[];
     constexpr int KPL = 2 * L;
     constexpr int TM_COLS = kV4Slots * kV4SlotCols;   // 256
     unsigned char *ring = smem;

@@ -40,8 +40,6 @@ struct BlindRotateArgs {
     int32_t mu;               // test-vector value (2^29 for gates)
     int32_t *u;               // out: [items][N+1]
     int64_t items;
-    int pair;                 // 1: warps g and g+4 alternate transform / non-transform blocks
-    int stagger;              // clocks between the start of successive warps of a CTA (set by the launcher)
 };
 constexpr int kOpRaw = 100;
 

@@ -373,12 +373,6 @@ __global__ void __maxnreg__(255) k_blind_rotate(const DeviceKey key, const Blind
     const RootSet w2 = load_rootset(c_tw.p2[t >> 3]), w3 = load_rootset(c_tw.p3[t]);
     const NamedBarrier64 bar{1 + g};
     bar();
-    // Groups that share SM sub-partitions (g and g+2) run the same instruction stream; started together
-    // they collide on the FP64 and shared-memory pipes phase by phase.  Offset the second pair.
-    if (a.stagger > 0 && G > 2 && g >= 2) {
-        const long long until = clock64() + (long long)a.stagger;
-        while (clock64() < until) {}
-    }
 
     // ---- blind rotation (lwe-bootstrapping-functions-fft.cpp:88-112)
     RingRows<STAGES> rows{ring, st, key.bkfft, 0, total, 2 * G};
@@ -634,24 +628,14 @@ static cudaError_t br_launch_st(const DeviceKey &key, const BlindRotateArgs &a, 
         if (dev < 16) done[dev] = true;
     }
     const unsigned grid = (unsigned)((a.items + G - 1) / G);
-    static int stagger = -1;
-    if (stagger < 0) { const char *e = getenv("B200_STAGGER"); stagger = e ? atoi(e) : 0; }
-    BlindRotateArgs a2 = a;
-    a2.stagger = stagger;
-    k_blind_rotate<L, BGBIT, G, STAGES><<<grid, 64 * G, br_smem_bytes(G, STAGES), s>>>(key, a2);
+    k_blind_rotate<L, BGBIT, G, STAGES><<<grid, 64 * G, br_smem_bytes(G, STAGES), s>>>(key, a);
     return cudaSuccess;
 }
 // Ring depth: 7 stages for the 4-ciphertext CTA (everything that fits in 227 KB; 1.9 % faster than 4),
 // 2 stages for the one-ciphertext CTA of small batches so that three of them fit on an SM.
 template <int L, int BGBIT, int G>
 static cudaError_t br_launch(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
-    static int st = -1;
-    if (st < 0) { const char *ev = getenv("B200_STAGES"); st = ev ? atoi(ev) : 0; }
-    if (G == 4) {
-        if (st == 4) return br_launch_st<L, BGBIT, G, 4>(key, a, s);
-        return br_launch_st<L, BGBIT, G, 7>(key, a, s);
-    }
-    if (st == 4) return br_launch_st<L, BGBIT, G, 4>(key, a, s);
+    if (G == 4) return br_launch_st<L, BGBIT, G, 7>(key, a, s);
     return br_launch_st<L, BGBIT, G, 2>(key, a, s);
 }
 // Kernel choice: 0 = 64 threads per ciphertext (default), 1 = warp per ciphertext with TMEM accumulators
@@ -679,25 +663,7 @@ static cudaError_t br16_launch(const DeviceKey &key, const BlindRotateArgs &a, c
         if (dev < 16) done[dev] = true;
     }
     const unsigned grid = (unsigned)((a.items + G - 1) / G);
-    static int stagger = -1, pad = -1;
-    if (pad < 0) {
-        const char *e = getenv("B200_SMEM_PAD");   // experiments: force one CTA per SM
-        pad = e ? atoi(e) : 0;
-        if (pad) cudaFuncSetAttribute(k_blind_rotate16<L, BGBIT, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    }
-    if (stagger < 0) {
-        const char *e = getenv("B200_STAGGER");
-        stagger = e ? atoi(e) : 0;
-    }
-    static int pair = -1;
-    if (pair < 0) {
-        const char *e = getenv("B200_PAIR");
-        pair = e ? atoi(e) : 0;
-    }
-    BlindRotateArgs a2 = a;
-    a2.stagger = stagger;
-    a2.pair = pair;
-    k_blind_rotate16<L, BGBIT, G><<<grid, 32 * G, pad ? 200 * 1024 : br16_smem_bytes(G), s>>>(key, a2);
+    k_blind_rotate16<L, BGBIT, G><<<grid, 32 * G, br16_smem_bytes(G), s>>>(key, a);
     return cudaSuccess;
 }
 cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
@@ -760,10 +726,7 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         // the GPU that way, otherwise one warp per CTA so that small batches spread over all SMs.
         const bool wide16 = a.items >= 148 * 4;
         cudaError_t e16;
-        static int gsel = -1;
-        if (gsel < 0) { const char *e = getenv("B200_G"); gsel = e ? atoi(e) : 0; }
-#define BR16_LAUNCH(L_, B_) e16 = gsel == 4 ? br16_launch<L_, B_, 4>(key, a, s) : gsel == 2 ? br16_launch<L_, B_, 2>(key, a, s) : \
-                                  gsel == 1 ? br16_launch<L_, B_, 1>(key, a, s) : wide16 ? br16_launch<L_, B_, 8>(key, a, s) : br16_launch<L_, B_, 1>(key, a, s)
+#define BR16_LAUNCH(L_, B_) e16 = wide16 ? br16_launch<L_, B_, 8>(key, a, s) : br16_launch<L_, B_, 1>(key, a, s)
         if (key.l == 2 && key.Bgbit == 10) BR16_LAUNCH(2, 10);
         else if (key.l == 3 && key.Bgbit == 7) BR16_LAUNCH(3, 7);
         else if (key.l == 2 && key.Bgbit == 8) BR16_LAUNCH(2, 8);
