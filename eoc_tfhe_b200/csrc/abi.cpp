@@ -348,20 +348,23 @@ static int gate_batch_host_locked(b200_key *k, int op, int32_t *out, const int32
     if (k->out.ensure(bytes)) return 1;
     // Large bootstrapped batches: slice the batch so that the upload of slice i+1 and the download of slice
     // i-1 overlap the kernels of slice i (three streams).  A slice is a whole number of blind-rotation waves
-    // (148 SMs x 4 ciphertexts x 4) and of 64-sample key-switch tiles.  Snapshot semantics hold: every input
+    // (148 SMs x 6 ciphertexts) and of 64-sample key-switch tiles.  Snapshot semantics hold: every input
     // byte is read from the caller's buffers into the device staging copies, never from `out`.
-    constexpr int64_t kSliceQuantum = 148 * 4 * 4;
+    // whole waves of the 6-ciphertext blind-rotation CTAs (888) and, for big batches, of the 64-sample key-switch
+    // CTAs as well (148 x lcm(6, 64) = 28,416); smaller batches settle for whole 64-sample tiles (7,104)
+    constexpr int64_t kSliceSmall = 148 * 6 * 8, kSliceBig = 148 * 192;
+    const int64_t kSliceQuantum = count >= 2 * kSliceBig ? kSliceBig : kSliceSmall;
     // (an output that overlaps an input at a different offset would break that, so such calls are not sliced)
     auto shifted_overlap = [&](const int32_t *in) {
         if (!in || in == out) return false;
         const char *i0 = (const char *)in, *o0 = (const char *)out;
         return i0 < o0 + bytes && o0 < i0 + bytes;
     };
-    if (!op_is_linear(op) && !nonzero && count >= 4 * kSliceQuantum && !shifted_overlap(a) && !shifted_overlap(b) &&
+    if (!op_is_linear(op) && !nonzero && count >= 2 * kSliceSmall && !shifted_overlap(a) && !shifted_overlap(b) &&
         !shifted_overlap(need_c ? c : nullptr)) {
         const int n1 = d.n + 1;
-        int64_t slice = (count + b200_key::kSlices - 1) / b200_key::kSlices;
-        slice = (slice + kSliceQuantum - 1) / kSliceQuantum * kSliceQuantum;
+        int64_t slice = std::max<int64_t>(1, (count / 4 + kSliceQuantum / 2) / kSliceQuantum) * kSliceQuantum;   // about a quarter, at least one quantum
+        while ((count + slice - 1) / slice > b200_key::kSlices) slice += kSliceQuantum;
         if (k->in0.ensure(bytes) || k->in1.ensure(bytes) || (need_c && k->in2.ensure(bytes))) return 1;
         CK(cudaEventRecord(k->ev_up[0], s));                 // order after earlier work on the key's stream
         CK(cudaStreamWaitEvent(k->stream_h2d, k->ev_up[0], 0));

@@ -63,7 +63,7 @@ struct b200_key {
     bool filled = false;
     cudaStream_t stream = nullptr;      // used by the *_host entries
     // host batches are pipelined in slices: uploads, kernels and downloads run on three streams
-    static constexpr int kSlices = 4;
+    static constexpr int kSlices = 8;
     cudaStream_t stream_h2d = nullptr, stream_d2h = nullptr;
     cudaEvent_t ev_up[kSlices] = {}, ev_done[kSlices] = {};
     std::mutex mu;                      // one call at a time per key (shared workspace)

@@ -308,7 +308,7 @@ constexpr int kCmuxTestSmemBytes = kGroupSmemBytes;
 // G ciphertexts per CTA (64 threads each), walking i = 0..n-1 in lockstep on one TMA-fed ring of
 // bootstrapping-key row pairs.  Groups synchronise among themselves with named barriers only.
 template <int L, int BGBIT, int G, int STAGES = kBrStages>
-__global__ void __maxnreg__(255) k_blind_rotate(const DeviceKey key, const BlindRotateArgs a) {
+__global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key, const BlindRotateArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr int KPL = 2 * L;
     unsigned char *ring = smem;                                                       // [stages][16 KiB]
@@ -631,12 +631,13 @@ static cudaError_t br_launch_st(const DeviceKey &key, const BlindRotateArgs &a, 
     k_blind_rotate<L, BGBIT, G, STAGES><<<grid, 64 * G, br_smem_bytes(G, STAGES), s>>>(key, a);
     return cudaSuccess;
 }
-// Ring depth: 7 stages for the 4-ciphertext CTA (everything that fits in 227 KB; 1.9 % faster than 4),
+// Ring depth: 3 stages for the 6-ciphertext CTA, 7 for the 4-ciphertext CTA (everything that fits in 227 KB),
 // 2 stages for the one-ciphertext CTA of small batches so that three of them fit on an SM.
 template <int L, int BGBIT, int G>
 static cudaError_t br_launch(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
-    if (G == 4) return br_launch_st<L, BGBIT, G, 7>(key, a, s);
-    return br_launch_st<L, BGBIT, G, 2>(key, a, s);
+    if constexpr (G == 6) return br_launch_st<L, BGBIT, G, 3>(key, a, s);
+    else if constexpr (G == 4) return br_launch_st<L, BGBIT, G, 7>(key, a, s);
+    else return br_launch_st<L, BGBIT, G, 2>(key, a, s);
 }
 // Kernel choice: 0 = 64 threads per ciphertext (default), 1 = warp per ciphertext with TMEM accumulators
 // (B200_BR_KERNEL=w16 or b200_set_blind_rotate_kernel(1)).
@@ -739,7 +740,13 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
     }
     const bool wide = a.items >= 148 * 4;
     cudaError_t e;
+    // l = 2: six groups per CTA (12 warps, 168 registers, 3-stage ring) are 1.9 % faster than four (8 warps,
+    // 246 registers, 7 stages); at l = 3 they are 3 % slower (636.6 vs 617.2 ms per 65,536).  B200_G6=0: four.
+    static int g6 = -1;
+    if (g6 < 0) { const char *ev = getenv("B200_G6"); g6 = ev ? atoi(ev) : 1; }
 #define BR_LAUNCH(L_, B_) e = wide ? br_launch<L_, B_, 4>(key, a, s) : br_launch<L_, B_, 1>(key, a, s)
+    if (g6 && a.items >= 148 * 6 && key.l == 2 && key.Bgbit == 10) e = br_launch<2, 10, 6>(key, a, s);
+    else
     if (key.l == 2 && key.Bgbit == 10) BR_LAUNCH(2, 10);
     else if (key.l == 3 && key.Bgbit == 7) BR_LAUNCH(3, 7);
     else if (key.l == 2 && key.Bgbit == 8) BR_LAUNCH(2, 8);
