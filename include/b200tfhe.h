@@ -302,9 +302,12 @@ int  b200_fp64_peak_tflops(int device, double *tflops);
 /* Blind-rotation kernel used by subsequent calls: 0 = 64 threads per ciphertext, accumulators in
  * registers (default); 1 = one warp per ciphertext, 16-point transforms, accumulators in tensor memory
  * (tcgen05.ld/st); 2..6 = the 64-thread layout with accumulators in tensor memory (2: 6 groups per SM,
- * 3: 4 groups of two ciphertexts sharing every key read, 4..6: other group shapes), bit-identical to 0.
- * All produce results within the same bounds; the choice is a performance knob that bench.py and the
- * parity tests exercise.  Also settable with B200_BR_KERNEL=v2|w16|<number> before first use. */
+ * 3: 4 groups of two ciphertexts sharing every key read, 4..6: other group shapes); 7 = key rows staged
+ * TMA -> shared memory -> tcgen05.cp -> tensor memory, read by the spectral MAC with tcgen05.ld; 8 = two
+ * warps per ciphertext, warp h owning accumulator polynomial h, 16-point transforms (l = 2 only, wide
+ * batches; falls back to 0 otherwise).  Every variant is bit-identical to 0; the
+ * choice is a performance knob that bench.py and the parity tests exercise.  Batches of at most one
+ * ciphertext per SM use the latency kernel (one ciphertext per CTA) while the variant is 0.  Also settable with B200_BR_KERNEL=v2|w16|<number> before first use. */
 int  b200_set_blind_rotate_kernel(int variant);
 /* Key-switch kernel: 0 = chosen by batch size (default), 1 = gather kernel (8-sample tiles, any batch),
  * 2 = table-streaming kernel (64 samples per CTA, table rows staged by TMA).  Results are identical. */
