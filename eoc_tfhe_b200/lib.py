@@ -66,6 +66,15 @@ SIGNATURES = {
     "b200_set_blind_rotate_kernel": (C.c_int, [C.c_int]),
     "b200_set_keyswitch_kernel": (C.c_int, [C.c_int]),
     "bootsGate_batch": (C.c_int, [C.c_int, _VP, _VP, _VP, _VP, C.c_int32, _VP]),
+    # eoc evaluation-side entry points (csrc/eoc_abi.cpp); strings come back as new[] pointers
+    "addCiphertexts": (_VP, [C.c_char_p, C.c_char_p, C.c_char_p]),
+    "subtractCiphertexts": (_VP, [C.c_char_p, C.c_char_p, C.c_char_p]),
+    "addCiphertextBits": (_VP, [C.c_char_p, C.c_char_p, C.c_int32]),
+    "subtractCiphertextBits": (_VP, [C.c_char_p, C.c_char_p, C.c_int32]),
+    "b200_eoc_free": (None, [_VP]),
+    "b200_eoc_set_cloud_key": (C.c_int, [C.c_char_p]),
+    "b200_eoc_set_key": (C.c_int, [_VP]),
+    "b200_add_bits_host": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int32, C.c_int64, C.c_int]),
 }
 for _g in ("NAND", "OR", "AND", "XOR", "XNOR", "NOR", "ANDNY", "ANDYN", "ORNY", "ORYN"):
     SIGNATURES["boots" + _g] = (None, [_VP, _VP, _VP, _VP])

@@ -262,6 +262,36 @@ int  b200_level_run_dev(b200_key *key, int32_t *d_wires, const int32_t *rot_desc
                         const int32_t *ks_desc, int64_t n_ks, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * eoc evaluation-side entry points (ao-tfhe/eoc-tfhe-run.cpp).  Key generation,
+ * encryption and decryption need the secret key and stay in the reference.
+ * ------------------------------------------------------------------------------------------ */
+/* eoc-tfhe-run.cpp:427-469 / :472-513: base64(LweSample record) x 2 -> base64(record of the sum /
+ * difference): lweCopy + lweAddTo / lweSubTo, int32 wrap-around, variances add.  Host integer work,
+ * bit-exact.  The third argument is ignored, as in the reference.  Returns a new[] string (release it
+ * with b200_eoc_free) or NULL with the message on stderr and in b200_last_error().  Unlike the
+ * reference no key has to be loaded first: the dimension n comes from the record length. */
+const char *addCiphertexts     (const char *base64Ciphertext1, const char *base64Ciphertext2, const char *base64PublicKey);
+const char *subtractCiphertexts(const char *base64Ciphertext1, const char *base64Ciphertext2, const char *base64PublicKey);
+void b200_eoc_free(const char *s);
+/* Evaluation key of the bit-sliced entry points below: base64 of what
+ * export_tfheGateBootstrappingCloudKeySet_toStream writes (the library owns the device key), or an
+ * existing handle (not owned).  Mirrors eoc's process-global key (eoc-tfhe-run.cpp:38-39). */
+int  b200_eoc_set_cloud_key(const char *base64_cloud_key);
+int  b200_eoc_set_key(b200_key *key);
+/* Integers encrypted bit by bit (LSB first, one gate-bootstrapping ciphertext per bit, as
+ * test-addition-boot.cpp:190-197) added / subtracted with the bootstrapped ripple-carry adder
+ * (full_adder, test-addition-boot.cpp:70-94; x - y = x + ~y + 1), every depth level of all `count`
+ * operand pairs as one launch pair.  x, y: [count][nb_bits][n+1]; sum: [count][nb_bits+1][n+1], bit
+ * nb_bits = carry out (subtract: 1 = no borrow). */
+int  b200_add_bits_host(b200_key *key, int32_t *sum, const int32_t *x, const int32_t *y, int32_t nb_bits,
+                        int64_t count, int subtract);
+/* The same for one pair of base64 strings holding nb_bits concatenated sample records; returns
+ * nb_bits + 1 records (variance fields 0).  NULL + stderr message when no key is set (as
+ * eoc-tfhe-run.cpp:464-468) or the operands do not match the key's dimension. */
+const char *addCiphertextBits     (const char *base64X, const char *base64Y, int32_t nb_bits);
+const char *subtractCiphertextBits(const char *base64X, const char *base64Y, int32_t nb_bits);
+
+/* ------------------------------------------------------------------------------------------
  * libtfhe wire format (host only, no device needed except b200_key_from_cloudkey_*): what
  * export_tfheGateBootstrappingCloudKeySet_toFile and export_gate_bootstrapping_ciphertext_toFile
  * write (libs/tfhe/src/libtfhe/tfhe_io.cpp:90-107,757-785,883-905,1031-1035,1099-1103).
