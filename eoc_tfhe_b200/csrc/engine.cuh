@@ -40,6 +40,9 @@ struct BlindRotateArgs {
     int32_t mu;               // test-vector value (2^29 for gates)
     int32_t *u;               // out: [items][N+1]
     int64_t items;
+    // balanced grid of the multi-ciphertext CTA (set by the launcher): CTA b owns bal_q + (b < bal_r)
+    // consecutive items; bal_q == 0: CTA b owns items [b*G, b*G + G)
+    int bal_q = 0, bal_r = 0;
 };
 constexpr int kOpRaw = 100;
 

@@ -320,8 +320,9 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
     uint16_t *bara = reinterpret_cast<uint16_t *>(mine + 2 * kN * 4 + 2 * kBufElems * 16);  // [n+1]
 
     const int n = key.n, n1 = n + 1;
-    const int64_t item = (int64_t)blockIdx.x * G + g;
-    const bool live = item < a.items;
+    const int bmin = min((int)blockIdx.x, a.bal_r);
+    const int64_t item = a.bal_q ? (int64_t)blockIdx.x * a.bal_q + bmin + g : (int64_t)blockIdx.x * G + g;
+    const bool live = a.bal_q ? g < a.bal_q + ((int)blockIdx.x < a.bal_r) : item < a.items;
     const int total = n * KPL;
 
     if (threadIdx.x == 0) {
@@ -614,8 +615,21 @@ cudaError_t launch_ks_pack(const DeviceKey &key, const int32_t *d_ks_rows, cudaS
     return cudaGetLastError();
 }
 
-// Ciphertexts per CTA: 4 (one CTA per SM, one key read per 4 ciphertexts) once the batch fills the
-// GPU that way, otherwise 1 so that small batches still spread over all SMs.
+// Ciphertexts per CTA: up to 4 or 6 (one CTA per SM, one key read per CTA) as soon as the batch has more than
+// one ciphertext per SM -- spread evenly over whole waves of CTAs, see below; 1 only when the latency
+// kernel is switched off (B200_LAT=0).
+static int sm_count_of(int dev) {
+    static int cached[16] = {0};
+    if (dev < 16 && cached[dev]) return cached[dev];
+    int v = 148;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    if (dev < 16) cached[dev] = v;
+    return v;
+}
+static bool br_balance() {
+    static const bool on = [] { const char *e = getenv("B200_BALANCE"); return !(e && e[0] == '0'); }();
+    return on;
+}
 template <int L, int BGBIT, int G, int STAGES>
 static cudaError_t br_launch_st(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
     static bool done[16] = {false};
@@ -627,8 +641,20 @@ static cudaError_t br_launch_st(const DeviceKey &key, const BlindRotateArgs &a, 
         cudaFuncSetAttribute(k_blind_rotate<L, BGBIT, G, STAGES>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         if (dev < 16) done[dev] = true;
     }
-    const unsigned grid = (unsigned)((a.items + G - 1) / G);
-    k_blind_rotate<L, BGBIT, G, STAGES><<<grid, 64 * G, br_smem_bytes(G, STAGES), s>>>(key, a);
+    unsigned grid = (unsigned)((a.items + G - 1) / G);
+    BlindRotateArgs b = a;
+    if (G > 1 && br_balance()) {
+        // whole waves of one CTA per SM, items spread evenly over them: the last wave then runs CTAs
+        // with fewer ciphertexts (which finish sooner) on every SM instead of full CTAs on a few
+        const int64_t sms = sm_count_of(dev);
+        const int64_t even = (grid + sms - 1) / sms * sms;
+        if (even <= a.items) {
+            grid = (unsigned)even;
+            b.bal_q = (int)(a.items / even);
+            b.bal_r = (int)(a.items % even);
+        }
+    }
+    k_blind_rotate<L, BGBIT, G, STAGES><<<grid, 64 * G, br_smem_bytes(G, STAGES), s>>>(key, b);
     return cudaSuccess;
 }
 // Ring depth: 3 stages for the 6-ciphertext CTA, 7 for the 4-ciphertext CTA (everything that fits in 227 KB),
@@ -738,14 +764,17 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         COUNT_LAUNCH();
         return cudaGetLastError();
     }
-    const bool wide = a.items >= 148 * 4;
+    // More than one ciphertext per SM: multi-ciphertext CTAs on a balanced grid (br_launch_st).  Measured at
+    // l = 2 (ms, G=1 x 3 CTAs per SM / G=4 / G=6): 296 items 2.39 / 2.29 / 2.66; 591: 4.69 / 3.44 / 3.73;
+    // 600: - / 5.49 / 4.74; 887: - / 6.48 / 4.92.
+    const bool wide = a.items > 148;
     cudaError_t e;
     // l = 2: six groups per CTA (12 warps, 168 registers, 3-stage ring) are 1.9 % faster than four (8 warps,
     // 246 registers, 7 stages); at l = 3 they are 3 % slower (636.6 vs 617.2 ms per 65,536).  B200_G6=0: four.
     static int g6 = -1;
     if (g6 < 0) { const char *ev = getenv("B200_G6"); g6 = ev ? atoi(ev) : 1; }
 #define BR_LAUNCH(L_, B_) e = wide ? br_launch<L_, B_, 4>(key, a, s) : br_launch<L_, B_, 1>(key, a, s)
-    if (g6 && a.items >= 148 * 6 && key.l == 2 && key.Bgbit == 10) e = br_launch<2, 10, 6>(key, a, s);
+    if (g6 && a.items > 148 * 4 && key.l == 2 && key.Bgbit == 10) e = br_launch<2, 10, 6>(key, a, s);
     else
     if (key.l == 2 && key.Bgbit == 10) BR_LAUNCH(2, 10);
     else if (key.l == 3 && key.Bgbit == 7) BR_LAUNCH(3, 7);
