@@ -331,3 +331,58 @@ def test_random_gate_stream_with_dependencies(p80):
     plain = nl.evaluate_plain({w: bits[:, i] for i, w in enumerate(ins)})
     want = np.stack([np.broadcast_to(np.asarray(plain[w]), (count,)) for w in nl.outputs["y"]], axis=1)
     assert np.array_equal(got, want)
+
+
+def test_batch_sizes_across_every_kernel_boundary(p80):
+    """Ragged batches: sizes on both sides of every dispatch boundary (latency kernel <= 148, four ciphertexts
+    per CTA <= 592, six above; balanced grids with q, q+1 ciphertexts per CTA; gather / streaming key switch)
+    give, gate for gate, the words of one large batch -- a gate's output depends on its inputs only.  An empty
+    batch is a no-op."""
+    import torch
+    from eoc_tfhe_b200 import GateOp
+    rk, ck = p80
+    rng = np.random.default_rng(2024)
+    total = 148 * 21 + 5      # > 2,960: the large batch itself takes the streaming key switch
+    bits_a, bits_b = rng.integers(0, 2, size=total).astype(np.int32), rng.integers(0, 2, size=total).astype(np.int32)
+    pool = rk.encrypt_bits(np.array([0, 1], dtype=np.int32))
+    noise = rng.integers(-(1 << 20), 1 << 20, size=(2, total, rk.n + 1), dtype=np.int64).astype(np.int32)
+    noise[:, :, :rk.n] = 0    # distinct ciphertexts of the same bits: perturb b well inside the margin
+    a = torch.from_numpy(pool[bits_a] + noise[0]).cuda()
+    b = torch.from_numpy(pool[bits_b] + noise[1]).cuda()
+    want = ck.gate(GateOp.XOR, a, b)
+    assert np.array_equal(rk.decrypt_bits(want.cpu().numpy()), bits_a ^ bits_b)
+    for count in (1, 2, 147, 148, 149, 150, 295, 297, 445, 591, 592, 593, 739, 887, 888, 889, 1037, 148 * 20 - 1, 148 * 20):
+        got = ck.gate(GateOp.XOR, a[:count], b[:count])
+        assert torch.equal(got, want[:count]), count
+    out = torch.full((4, rk.n + 1), 7, dtype=torch.int32, device="cuda")
+    ck.gate(GateOp.XOR, a[:0], b[:0], out=out[:0])
+    assert int((out != 7).sum()) == 0
+
+
+def test_noiseless_inputs_equal_reference_word_for_word(p80):
+    """Trivial (noiseless) samples have a = 0: every bara_i is 0, all CMux steps are skipped
+    (lwe-bootstrapping-functions-fft.cpp:101) and the whole gate is integer work -- prologue, modulus switch of
+    b, test-vector rotation, extraction, key switch.  Output CIPHERTEXTS therefore equal libtfhe's exactly, for
+    every gate type and every b that lands in a different rotation."""
+    import torch
+    from eoc_tfhe_b200 import GateOp
+    rk, ck = p80
+    rng = np.random.default_rng(31)
+    count = 160
+    a = np.zeros((count, rk.n + 1), dtype=np.int32)
+    b = np.zeros_like(a)
+    a[:, rk.n] = rng.integers(-2**31, 2**31, size=count, dtype=np.int64).astype(np.int32)
+    b[:, rk.n] = rng.integers(-2**31, 2**31, size=count, dtype=np.int64).astype(np.int32)
+    a[0, rk.n], b[0, rk.n] = 1 << 29, 1 << 29
+    a[1, rk.n], b[1, rk.n] = -(1 << 29), 1 << 29
+    a[2, rk.n], b[2, rk.n] = 0, 0
+    ta, tb = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+    for name in ("NAND", "XOR", "ORYN", "ANDNY"):
+        want, _ = rk.gate_mt(name, a, b)
+        got = ck.gate(GateOp[name], ta, tb).cpu().numpy()
+        assert np.array_equal(got, want), name
+    c = np.zeros_like(a)
+    c[:, rk.n] = rng.integers(-2**31, 2**31, size=count, dtype=np.int64).astype(np.int32)
+    want, _ = rk.gate_mt("MUX", a[:48], b[:48], c[:48])
+    got = ck.gate(GateOp.MUX, ta[:48], tb[:48], torch.from_numpy(c[:48]).cuda()).cpu().numpy()
+    assert np.array_equal(got, want)
