@@ -352,8 +352,10 @@ def test_batch_sizes_across_every_kernel_boundary(p80):
     want = ck.gate(GateOp.XOR, a, b)
     assert np.array_equal(rk.decrypt_bits(want.cpu().numpy()), bits_a ^ bits_b)
     for count in (1, 2, 147, 148, 149, 150, 295, 297, 445, 591, 592, 593, 739, 887, 888, 889, 1037, 148 * 20 - 1, 148 * 20):
-        got = ck.gate(GateOp.XOR, a[:count], b[:count])
-        assert torch.equal(got, want[:count]), count
+        buf = torch.full((count + 2, rk.n + 1), 0x5A5A5A5A, dtype=torch.int32, device="cuda")   # guard rows
+        ck.gate(GateOp.XOR, a[:count], b[:count], out=buf[1:count + 1])
+        assert torch.equal(buf[1:count + 1], want[:count]), count
+        assert bool((buf[0] == 0x5A5A5A5A).all()) and bool((buf[-1] == 0x5A5A5A5A).all()), count
     out = torch.full((4, rk.n + 1), 7, dtype=torch.int32, device="cuda")
     ck.gate(GateOp.XOR, a[:0], b[:0], out=out[:0])
     assert int((out != 7).sum()) == 0
