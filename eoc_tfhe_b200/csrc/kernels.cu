@@ -774,8 +774,33 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
     static int g6 = -1;
     if (g6 < 0) { const char *ev = getenv("B200_G6"); g6 = ev ? atoi(ev) : 1; }
 #define BR_LAUNCH(L_, B_) e = wide ? br_launch<L_, B_, 4>(key, a, s) : br_launch<L_, B_, 1>(key, a, s)
-    if (g6 && a.items > 148 * 4 && key.l == 2 && key.Bgbit == 10) e = br_launch<2, 10, 6>(key, a, s);
-    else
+    if (g6 && a.items > 148 * 4 && key.l == 2 && key.Bgbit == 10) {
+        // A wave of the six-group kernel takes about as long with four groups per CTA as with six (4.74 vs
+        // 4.92 ms), a wave of the four-group kernel 3.44 ms (2.3 ms at two per CTA) and the latency kernel
+        // 1.35 ms: when what is left after whole six-group waves fits one narrower wave, it goes there.
+        int dev = 0;
+        cudaGetDevice(&dev);
+        const int64_t wave6 = (int64_t)sm_count_of(dev) * 6, rest = a.items % wave6;
+        if (br_balance() && a.items > wave6 && rest > 0 && rest <= (int64_t)sm_count_of(dev) * 4) {
+            const int64_t head = a.items - rest;
+            BlindRotateArgs h = a, r = a;
+            h.items = head;
+            r.items = rest;
+            r.u += (size_t)head * (kN + 1);
+            if (a.desc) r.desc += head;
+            else {
+                const size_t rows = (size_t)(a.op == B200_MUX ? head / 2 : head) * (key.n + 1);   // wave6 is even
+                if (r.in0) r.in0 += rows;
+                if (r.in1) r.in1 += rows;
+                if (r.in2) r.in2 += rows;
+            }
+            e = br_launch<2, 10, 6>(key, h, s);
+            if (e != cudaSuccess) return e;
+            COUNT_LAUNCH();
+            return launch_blind_rotate(key, r, s);
+        }
+        e = br_launch<2, 10, 6>(key, a, s);
+    } else
     if (key.l == 2 && key.Bgbit == 10) BR_LAUNCH(2, 10);
     else if (key.l == 3 && key.Bgbit == 7) BR_LAUNCH(3, 7);
     else if (key.l == 2 && key.Bgbit == 8) BR_LAUNCH(2, 8);

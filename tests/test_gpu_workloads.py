@@ -356,6 +356,12 @@ def test_batch_sizes_across_every_kernel_boundary(p80):
         ck.gate(GateOp.XOR, a[:count], b[:count], out=buf[1:count + 1])
         assert torch.equal(buf[1:count + 1], want[:count]), count
         assert bool((buf[0] == 0x5A5A5A5A).all()) and bool((buf[-1] == 0x5A5A5A5A).all()), count
+    # MUX: two rotations per gate, so the boundaries sit at half the counts
+    c = torch.roll(a, 1, dims=0)
+    want_mux = ck.gate(GateOp.MUX, a, b, c)
+    for count in (1, 74, 75, 296, 297, 444, 445, 500, 888, 889, 1000):
+        got = ck.gate(GateOp.MUX, a[:count], b[:count], c[:count])
+        assert torch.equal(got, want_mux[:count]), ("MUX", count)
     out = torch.full((4, rk.n + 1), 7, dtype=torch.int32, device="cuda")
     ck.gate(GateOp.XOR, a[:0], b[:0], out=out[:0])
     assert int((out != 7).sum()) == 0
