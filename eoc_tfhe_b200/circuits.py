@@ -176,10 +176,21 @@ def run_batch(cloud_key, netlist, inputs, count, stream=None):
     gates, num_wires = netlist.replicate(count)
     first = next(iter(inputs.values()))
     if isinstance(first, np.ndarray):
-        pool = np.zeros((count, netlist.num_wires, n1), dtype=np.int32)
-        for name, wires in netlist.inputs.items():
-            pool[:, wires, :] = inputs[name]
-        levels = cloud_key.run_circuit(gates, pool.reshape(num_wires, n1))
+        # packed I/O: only input rows go up and output rows come back; the pool stays on the device
+        base = (np.arange(count, dtype=np.int64) * netlist.num_wires)[:, None]
+        in_names, out_names = list(netlist.inputs), list(netlist.outputs)
+        in_wires = np.concatenate([base + np.asarray(netlist.inputs[k])[None, :] for k in in_names], axis=1)
+        in_rows = np.concatenate([np.asarray(inputs[k], dtype=np.int32).reshape(count, -1, n1) for k in in_names], axis=1)
+        out_wires = np.concatenate([base + np.asarray(netlist.outputs[k])[None, :] for k in out_names], axis=1)
+        rows, levels = cloud_key.run_circuit_io(gates, num_wires, in_wires.astype(np.int32), in_rows.reshape(-1, n1),
+                                                out_wires.astype(np.int32))
+        rows = rows.reshape(count, -1, n1)
+        outs, at = {}, 0
+        for k in out_names:
+            w = len(netlist.outputs[k])
+            outs[k] = rows[:, at:at + w, :]
+            at += w
+        return outs, levels
     else:
         import torch
         pool = torch.zeros((count, netlist.num_wires, n1), dtype=torch.int32, device=first.device)

@@ -173,7 +173,7 @@ extern "C" void b200_key_free(b200_key *k) {
     if (k->stream) cudaStreamSynchronize(k->stream);
     if (k->dk.bkfft) cudaFree(k->dk.bkfft);
     if (k->dk.ks) cudaFree(k->dk.ks);
-    for (DevBuf *b : {&k->u, &k->in0, &k->in1, &k->in2, &k->out, &k->nz, &k->desc_rot, &k->desc_ks, &k->desc_lin, &k->acc}) b->release();
+    for (DevBuf *b : {&k->u, &k->in0, &k->in1, &k->in2, &k->out, &k->nz, &k->desc_rot, &k->desc_ks, &k->desc_lin, &k->desc_io, &k->acc}) b->release();
     k->stage_in.release();
     k->stage_out.release();
     for (auto &slot : k->ring)

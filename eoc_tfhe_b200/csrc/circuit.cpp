@@ -222,3 +222,49 @@ extern "C" int b200_circuit_run_host(b200_key *key, const int32_t *gates, int64_
     B200_CK(cudaStreamSynchronize(s));
     return 0;
 }
+
+// Packed I/O: the device pool is [num_wires | n_in staged input rows | n_out staged output rows]; inputs
+// are scattered into their wires and outputs gathered from theirs by row copies on the device, so the
+// host moves n_in + n_out rows instead of 2 x num_wires.
+extern "C" int b200_circuit_run_host_io(b200_key *key, const int32_t *gates, int64_t num_gates, int64_t num_wires,
+                                        const int32_t *in_wires, int64_t n_in, const int32_t *in_rows,
+                                        const int32_t *out_wires, int64_t n_out, int32_t *out_rows,
+                                        int32_t *levels_out) {
+    if (!key || !key->filled) return b200_fail("key is NULL or not filled");
+    if (!gates || num_wires <= 0 || n_in < 0 || n_out < 0 || (n_in && (!in_wires || !in_rows)) ||
+        (n_out && (!out_wires || !out_rows)))
+        return b200_fail("bad argument");
+    if (num_wires + n_in + n_out > 0x7fffffffLL) return b200_fail("wire pool too large");
+    std::vector<int32_t> desc((size_t)(n_in + n_out) * 4);
+    for (int64_t i = 0; i < n_in; ++i) {
+        if (in_wires[i] < 0 || in_wires[i] >= num_wires) return b200_fail("input wire out of range");
+        int32_t *d = &desc[(size_t)i * 4];
+        d[0] = B200_COPY; d[1] = in_wires[i]; d[2] = (int32_t)(num_wires + i); d[3] = 0;
+    }
+    for (int64_t i = 0; i < n_out; ++i) {
+        if (out_wires[i] < 0 || out_wires[i] >= num_wires) return b200_fail("output wire out of range");
+        int32_t *d = &desc[(size_t)(n_in + i) * 4];
+        d[0] = B200_COPY; d[1] = (int32_t)(num_wires + n_in + i); d[2] = out_wires[i]; d[3] = 0;
+    }
+    std::lock_guard<std::mutex> g(key->mu);
+    B200_CK(cudaSetDevice(key->dk.device));
+    const size_t row = (size_t)(key->dk.n + 1) * 4;
+    if (key->out.ensure((size_t)(num_wires + n_in + n_out) * row)) return 1;
+    if (key->desc_io.ensure(desc.size() * 4 + 16)) return 1;
+    cudaStream_t s = key->stream;
+    int32_t *pool = (int32_t *)key->out.p;
+    int32_t *d_desc = (int32_t *)key->desc_io.p;
+    B200_CK(cudaMemsetAsync(pool, 0, (size_t)num_wires * row, s));
+    if (!desc.empty()) B200_CK(cudaMemcpyAsync(d_desc, desc.data(), desc.size() * 4, cudaMemcpyHostToDevice, s));
+    if (n_in) {
+        B200_CK(cudaMemcpyAsync((char *)pool + (size_t)num_wires * row, in_rows, (size_t)n_in * row, cudaMemcpyHostToDevice, s));
+        B200_CK(b200::launch_linear_desc(key->dk, pool, d_desc, n_in, s));
+    }
+    if (circuit_run_locked(key, gates, num_gates, pool, num_wires, levels_out, s)) return 1;
+    if (n_out) {
+        B200_CK(b200::launch_linear_desc(key->dk, pool, d_desc + (size_t)n_in * 4, n_out, s));
+        B200_CK(cudaMemcpyAsync(out_rows, (char *)pool + (size_t)(num_wires + n_in) * row, (size_t)n_out * row, cudaMemcpyDeviceToHost, s));
+    }
+    B200_CK(cudaStreamSynchronize(s));
+    return 0;
+}

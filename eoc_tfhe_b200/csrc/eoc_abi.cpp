@@ -156,6 +156,7 @@ extern "C" int b200_add_bits_host(b200_key *key, int32_t *sum, const int32_t *x,
     int32_t nw = 0;
     ripple_netlist(nb_bits, subtract != 0, one, nw, outw);
     const int64_t per = (int64_t)one.size() / 5;
+    if ((int64_t)nw * count > 0x7fffffffLL) return b200_fail("too many operand pairs for one call");
     // `count` independent instances over one pool, instance-major, so that a level holds the gates of
     // that depth of every operand pair
     std::vector<int32_t> gates((size_t)per * 5 * count);
@@ -165,15 +166,18 @@ extern "C" int b200_add_bits_host(b200_key *key, int32_t *sum, const int32_t *x,
             row[0] = one[g * 5];
             for (int f = 1; f < 5; ++f) row[f] = one[g * 5 + f] < 0 ? -1 : (int32_t)(one[g * 5 + f] + c * nw);
         }
-    std::vector<int32_t> wires((size_t)count * nw * n1, 0);
+    // packed I/O: operand rows go up as they are (x bits, then y bits, per pair), sum rows come back
+    std::vector<int32_t> in_wires((size_t)count * 2 * nb_bits), out_wires((size_t)count * (nb_bits + 1));
+    std::vector<int32_t> in_rows((size_t)count * 2 * nb_bits * n1);
     for (int64_t c = 0; c < count; ++c) {
-        std::memcpy(&wires[(size_t)c * nw * n1], x + (size_t)c * nb_bits * n1, (size_t)nb_bits * n1 * 4);
-        std::memcpy(&wires[((size_t)c * nw + nb_bits) * n1], y + (size_t)c * nb_bits * n1, (size_t)nb_bits * n1 * 4);
+        for (int i = 0; i < 2 * nb_bits; ++i) in_wires[(size_t)c * 2 * nb_bits + i] = (int32_t)(c * nw + i);
+        for (int i = 0; i <= nb_bits; ++i) out_wires[(size_t)c * (nb_bits + 1) + i] = (int32_t)(c * nw + outw[i]);
+        std::memcpy(&in_rows[(size_t)c * 2 * nb_bits * n1], x + (size_t)c * nb_bits * n1, (size_t)nb_bits * n1 * 4);
+        std::memcpy(&in_rows[((size_t)c * 2 + 1) * nb_bits * n1], y + (size_t)c * nb_bits * n1, (size_t)nb_bits * n1 * 4);
     }
-    if (b200_circuit_run_host(key, gates.data(), per * count, wires.data(), (int64_t)nw * count, nullptr)) return 1;
-    for (int64_t c = 0; c < count; ++c)
-        for (int i = 0; i <= nb_bits; ++i)
-            std::memcpy(sum + ((size_t)c * (nb_bits + 1) + i) * n1, &wires[((size_t)c * nw + outw[i]) * n1], n1 * 4);
+    if (b200_circuit_run_host_io(key, gates.data(), per * count, (int64_t)nw * count, in_wires.data(), (int64_t)in_wires.size(),
+                                 in_rows.data(), out_wires.data(), (int64_t)out_wires.size(), sum, nullptr))
+        return 1;
     return 0;
 }
 

@@ -67,7 +67,7 @@ struct b200_key {
     cudaStream_t stream_h2d = nullptr, stream_d2h = nullptr;
     cudaEvent_t ev_up[kSlices] = {}, ev_done[kSlices] = {};
     std::mutex mu;                      // one call at a time per key (shared workspace)
-    DevBuf u, in0, in1, in2, out, nz, desc_rot, desc_ks, desc_lin, acc;
+    DevBuf u, in0, in1, in2, out, nz, desc_rot, desc_ks, desc_lin, desc_io, acc;
     PinnedBuf stage_in, stage_out;
     // ring of CUDA-event triplets (before blind rotation, between, after key switch), one per gate call
     static constexpr int kRing = 64;

@@ -251,6 +251,19 @@ class CloudKey:
                                               wires.shape[0], C.byref(lv), C.c_void_p(s)))
         return lv.value
 
+    def run_circuit_io(self, gates, num_wires, in_wires, in_rows, out_wires):
+        """Circuit with packed host I/O (b200_circuit_run_host_io): in_rows [len(in_wires)][n+1] numpy int32 go
+        to the wires in_wires; returns (rows of out_wires, bootstrapped levels)."""
+        gates = _np_i32(gates)
+        iw, ow = _np_i32(in_wires).ravel(), _np_i32(out_wires).ravel()
+        rows = _np_i32(in_rows, (iw.size, self.params.n + 1))
+        out = np.empty((ow.size, self.params.n + 1), dtype=np.int32)
+        lv = C.c_int32()
+        _lib.check(_lib.load().b200_circuit_run_host_io(self._h, gates.ctypes.data, gates.shape[0], int(num_wires),
+                                                        iw.ctypes.data, iw.size, rows.ctypes.data,
+                                                        ow.ctypes.data, ow.size, out.ctypes.data, C.byref(lv)))
+        return out, lv.value
+
     def run_level(self, wires, rot_desc, ks_desc, stream=None):
         """One level from launch descriptors (see b200_expand_gates) over a device wire pool."""
         import torch

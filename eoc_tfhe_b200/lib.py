@@ -47,6 +47,7 @@ SIGNATURES = {
     "b200_extern_product_host": (C.c_int, [_VP, _VP, C.c_int32, C.c_int64]),
     "b200_circuit_run_host": (C.c_int, [_VP, _VP, C.c_int64, _VP, C.c_int64, _I32P]),
     "b200_circuit_run_dev": (C.c_int, [_VP, _VP, C.c_int64, _VP, C.c_int64, _I32P, _VP]),
+    "b200_circuit_run_host_io": (C.c_int, [_VP, _VP, C.c_int64, C.c_int64, _VP, C.c_int64, _VP, _VP, C.c_int64, _VP, _VP]),
     "b200_circuit_levelize": (C.c_int, [_VP, C.c_int64, C.c_int64, _VP, _I32P]),
     "b200_expand_gates": (C.c_int, [_VP, C.c_int64, _VP, C.POINTER(C.c_int64), _VP, C.POINTER(C.c_int64)]),
     "b200_level_run_dev": (C.c_int, [_VP, _VP, _VP, C.c_int64, _VP, C.c_int64, _VP]),

@@ -246,6 +246,13 @@ int  b200_circuit_run_host(b200_key *key, const int32_t *gates, int64_t num_gate
                            int32_t *wires, int64_t num_wires, int32_t *levels_out);
 int  b200_circuit_run_dev (b200_key *key, const int32_t *gates, int64_t num_gates,
                            int32_t *d_wires, int64_t num_wires, int32_t *levels_out, void *stream);
+/* The same circuit with packed host I/O: only the rows of the listed input wires go up (in_rows
+ * [n_in][n+1] -> wires in_wires[i]) and only the listed output wires come back (out_rows [n_out][n+1]);
+ * the pool lives on the device only.  Wires that are neither written by a gate nor listed as inputs read
+ * as all-zero samples. */
+int  b200_circuit_run_host_io(b200_key *key, const int32_t *gates, int64_t num_gates, int64_t num_wires,
+                              const int32_t *in_wires, int64_t n_in, const int32_t *in_rows,
+                              const int32_t *out_wires, int64_t n_out, int32_t *out_rows, int32_t *levels_out);
 
 /* Host-only netlist helpers (no device needed): level of every gate (number of bootstrapped stages
  * before its output is ready; linear gates share the level of their input) and validation. */
