@@ -394,3 +394,34 @@ def test_noiseless_inputs_equal_reference_word_for_word(p80):
     want, _ = rk.gate_mt("MUX", a[:48], b[:48], c[:48])
     got = ck.gate(GateOp.MUX, ta[:48], tb[:48], torch.from_numpy(c[:48]).cuda()).cpu().numpy()
     assert np.array_equal(got, want)
+
+
+def test_circuit_entry_points_agree(p80):
+    """b200_circuit_run_host (whole pool up and down), b200_circuit_run_host_io (packed input / output rows)
+    and b200_circuit_run_dev (device pool) give the same output ciphertexts word for word, and the host pool
+    keeps its input rows."""
+    import torch
+    from eoc_tfhe_b200 import circuits
+    rk, ck = p80
+    nb, count = 4, 40
+    nl = circuits.full_adder_mux(nb)
+    rng = np.random.default_rng(8)
+    x, y = rng.integers(0, 1 << nb, size=count), rng.integers(0, 1 << nb, size=count)
+    cx = rk.encrypt_bits(circuits.int_to_bits(x, nb).ravel()).reshape(count, nb, -1)
+    cy = rk.encrypt_bits(circuits.int_to_bits(y, nb).ravel()).reshape(count, nb, -1)
+    gates, num_wires = nl.replicate(count)
+    pool = np.zeros((count, nl.num_wires, rk.n + 1), dtype=np.int32)
+    pool[:, nl.inputs["x"], :] = cx
+    pool[:, nl.inputs["y"], :] = cy
+    before = pool.copy()
+    levels = ck.run_circuit(gates, pool.reshape(num_wires, -1))
+    assert np.array_equal(pool[:, nl.inputs["x"], :], before[:, nl.inputs["x"], :])
+    want = pool[:, nl.outputs["sum"], :]
+    assert np.array_equal(circuits.bits_to_int(rk.decrypt_bits(want.reshape(-1, rk.n + 1)).reshape(count, nb + 1)), x + y)
+    outs, lv2 = circuits.run_batch(ck, nl, {"x": cx, "y": cy}, count)                       # packed I/O
+    assert lv2 == levels and np.array_equal(outs["sum"], want)
+    outs, lv3 = circuits.run_batch(ck, nl, {"x": torch.from_numpy(cx).cuda(), "y": torch.from_numpy(cy).cuda()}, count)
+    assert lv3 == levels and np.array_equal(outs["sum"].cpu().numpy(), want)
+    # out-of-range wires are refused
+    with pytest.raises(Exception):
+        ck.run_circuit_io(gates, num_wires, np.array([num_wires], dtype=np.int32), cx[0, :1], np.array([0], dtype=np.int32))
