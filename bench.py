@@ -333,6 +333,20 @@ def main_b200(args):
         ksm = sum(ks_ms) / len(ks_ms)
         achieved = count * FLOP_PER_BOOTSTRAP_P80 / (br * 1e-3) / 1e12
         ks_bytes = count * (6144 * n1 * 4 + (1024 + 1) * 4 + n1 * 4)  # 6144 table rows gathered per gate
+        # bootstrapping-key streaming (north_star: "achieved HBM/L2 GB/s on bootstrapping-key streaming"): every CTA of
+        # the blind rotation pulls the whole FFT-domain key (n x 2l row pairs of 16 KiB) from L2 through its TMA ring,
+        # once for the 6 ciphertexts it holds; the grid is whole waves of one CTA per SM (kernels.cu, br_launch_st)
+        sms = torch.cuda.get_device_properties(local).multi_processor_count
+        ctas = -(-(-(-count // 6)) // sms) * sms
+        key_bytes = P.n * 2 * P.l * 16384
+        tr = ncu_traffic("k_blind_rotate")
+        key_stream = {"kernel": "k_blind_rotate", "path": "L2 -> shared memory, cp.async.bulk ring", "ctas": ctas,
+                      "key_bytes": key_bytes, "bytes_per_launch": ctas * key_bytes,
+                      "achieved": ctas * key_bytes / (br * 1e-3) / 1e9, "unit": "GB/s",
+                      "unamortised": count * key_bytes / (br * 1e-3) / 1e9,
+                      "hbm_peak": hbm_peak, "frac_of_hbm_peak": ctas * key_bytes / (br * 1e-3) / 1e9 / hbm_peak,
+                      "dram_traffic_per_launch": tr,
+                      "note": "one key read serves 6 ciphertexts; the key (32.8 MB) stays L2 resident, so DRAM sees it about once per launch (traffic = inputs + extracted samples + key, ncu); 'unamortised' is what one read per ciphertext would need"}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -352,6 +366,7 @@ def main_b200(args):
                                    "unit": "GB/s", "frac": ks_bytes / (ksm * 1e-3) / 1e9 / hbm_peak, "traffic": ncu_traffic("k_keyswitch_tma"),
                                    "ms_per_launch": ksm, "share_of_step": ksm / ms_per_step, "peak_source": hbm_src,
                                    "note": "algorithmic bytes = naive per-gate gather of 6144 rows (SURVEY 8d); the kernel streams the table once per 64 samples through shared memory, so frac > 1 is expected: it is instruction-issue bound, see DESIGN.md 4.4"},
+            "key_stream": key_stream,
             "clocks": clocks,
             "key": {"upload_convert_s": key_upload_s, "nccl_broadcast_ms": key_bcast_ms,
                     "bytes": sum(n for _, n in ck.device_blobs())},

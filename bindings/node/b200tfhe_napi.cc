@@ -31,6 +31,8 @@ typedef int32_t Torus32;
 
 #include <string.h>
 
+#include <string>
+
 namespace {
 
 napi_value fail(napi_env env, const char *what) {
@@ -189,6 +191,63 @@ napi_value ReadSamples(napi_env env, napi_callback_info info) {
     return result;
 }
 
+// ---- eoc's string entry points (ao-tfhe/eoc-tfhe-run.cpp:427-513 and the bit-sliced counterparts) -------
+bool get_string(napi_env env, napi_value v, std::string *out) {
+    size_t len = 0;
+    if (napi_get_value_string_utf8(env, v, nullptr, 0, &len) != napi_ok) return false;
+    out->resize(len + 1);
+    if (napi_get_value_string_utf8(env, v, &(*out)[0], len + 1, &len) != napi_ok) return false;
+    out->resize(len);
+    return true;
+}
+
+// the reference returns nullptr on failure and the Lua/JS side sees nil (eoc-tfhe-bindings.c:128-148): null here
+napi_value take_string(napi_env env, const char *r) {
+    napi_value v;
+    if (!r) {
+        napi_get_null(env, &v);
+        return v;
+    }
+    napi_create_string_utf8(env, r, NAPI_AUTO_LENGTH, &v);
+    b200_eoc_free(r);
+    return v;
+}
+
+template <const char *(*FN)(const char *, const char *, const char *)>
+napi_value Linear(napi_env env, napi_callback_info info) {
+    size_t argc = 3;
+    napi_value argv[3];
+    napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+    std::string a, b;
+    if (argc < 2 || !get_string(env, argv[0], &a) || !get_string(env, argv[1], &b)) return fail(env, "(base64Ciphertext1, base64Ciphertext2[, base64PublicKey])");
+    return take_string(env, FN(a.c_str(), b.c_str(), ""));
+}
+
+template <const char *(*FN)(const char *, const char *, int32_t)>
+napi_value Bits(napi_env env, napi_callback_info info) {
+    size_t argc = 3;
+    napi_value argv[3];
+    napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+    std::string x, y;
+    int32_t nb = 0;
+    if (argc < 3 || !get_string(env, argv[0], &x) || !get_string(env, argv[1], &y) || napi_get_value_int32(env, argv[2], &nb) != napi_ok)
+        return fail(env, "(base64XBits, base64YBits, nbBits)");
+    return take_string(env, FN(x.c_str(), y.c_str(), nb));
+}
+
+// setCloudKeyBase64(string): evaluation key of the bit-sliced calls
+napi_value SetCloudKeyBase64(napi_env env, napi_callback_info info) {
+    size_t argc = 1;
+    napi_value argv[1];
+    napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+    std::string k;
+    if (argc < 1 || !get_string(env, argv[0], &k)) return fail(env, "setCloudKeyBase64(base64CloudKey)");
+    if (b200_eoc_set_cloud_key(k.c_str())) return fail(env, "setCloudKeyBase64");
+    napi_value u;
+    napi_get_undefined(env, &u);
+    return u;
+}
+
 void def(napi_env env, napi_value exports, const char *name, napi_callback cb) {
     napi_value fn;
     napi_create_function(env, name, NAPI_AUTO_LENGTH, cb, nullptr, &fn);
@@ -206,5 +265,10 @@ extern "C" __attribute__((visibility("default"))) napi_value napi_register_modul
     def(env, exports, "gateBatch", GateBatch);
     def(env, exports, "runCircuit", RunCircuit);
     def(env, exports, "readSamples", ReadSamples);
+    def(env, exports, "addCiphertexts", Linear<addCiphertexts>);
+    def(env, exports, "subtractCiphertexts", Linear<subtractCiphertexts>);
+    def(env, exports, "setCloudKeyBase64", SetCloudKeyBase64);
+    def(env, exports, "addCiphertextBits", Bits<addCiphertextBits>);
+    def(env, exports, "subtractCiphertextBits", Bits<subtractCiphertextBits>);
     return exports;
 }

@@ -38,6 +38,8 @@ napi_status napi_create_external(napi_env env, void *data, napi_finalize finaliz
 napi_status napi_get_value_external(napi_env env, napi_value value, void **result);
 napi_status napi_create_object(napi_env env, napi_value *result);
 napi_status napi_create_string_utf8(napi_env env, const char *str, size_t length, napi_value *result);
+napi_status napi_get_value_string_utf8(napi_env env, napi_value value, char *buf, size_t bufsize, size_t *result);
+napi_status napi_get_null(napi_env env, napi_value *result);
 napi_status napi_throw_error(napi_env env, const char *code, const char *msg);
 napi_status napi_get_undefined(napi_env env, napi_value *result);
 #ifdef __cplusplus
