@@ -425,3 +425,32 @@ def test_circuit_entry_points_agree(p80):
     # out-of-range wires are refused
     with pytest.raises(Exception):
         ck.run_circuit_io(gates, num_wires, np.array([num_wires], dtype=np.int32), cx[0, :1], np.array([0], dtype=np.int32))
+
+
+def test_host_entry_sliced_pipeline_equals_device_path(p80):
+    """b200_gate_batch_host pipelines large batches in slices over three streams (upload, kernels, download).
+    Ragged counts on both sides of the slicing threshold, an output buffer that IS an input buffer (snapshot
+    semantics, SURVEY 8b aliasing) and a three-input MUX give the words of the device-pointer entry."""
+    import torch
+    from eoc_tfhe_b200 import GateOp
+    rk, ck = p80
+    rng = np.random.default_rng(606)
+    total = 2 * 7104 + 2 * 7104 + 793
+    pool = rk.encrypt_bits(np.array([0, 1], dtype=np.int32))
+    bits = rng.integers(0, 2, size=(3, total)).astype(np.int32)
+    jitter = rng.integers(-(1 << 18), 1 << 18, size=(3, total), dtype=np.int64).astype(np.int32)
+    a, b, c = (pool[bits[i]].copy() for i in range(3))
+    for i, x in enumerate((a, b, c)):
+        x[:, rk.n] += jitter[i]
+    ta, tb, tc = (torch.from_numpy(x).cuda() for x in (a, b, c))
+    want = ck.gate(GateOp.ANDYN, ta, tb).cpu().numpy()
+    want_mux = ck.gate(GateOp.MUX, ta, tb, tc).cpu().numpy()
+    assert np.array_equal(rk.decrypt_bits(want[:4096]), (bits[0] & (1 - bits[1]))[:4096])
+    for count in (2 * 7104 - 1, 2 * 7104, 2 * 7104 + 1, total):
+        got = ck.gate(GateOp.ANDYN, a[:count], b[:count])
+        assert np.array_equal(got, want[:count]), count
+    got = ck.gate(GateOp.MUX, a, b, c)
+    assert np.array_equal(got, want_mux)
+    inplace = a.copy()
+    ck.gate(GateOp.ANDYN, inplace, b, out=inplace)       # out aliases the first input exactly
+    assert np.array_equal(inplace, want)
