@@ -18,5 +18,5 @@ for it in range(iters):
     ck.gate(GateOp.NAND, a, b, out=out)
     torch.cuda.synchronize()
     t = ck.timing_drain()
-    print(os.environ.get("B200_BR_KERNEL", "w16"), count, "items: blind_rotate %.3f ms, keyswitch %.3f ms" % (t["blind_rotate"], t["keyswitch"]), flush=True)
+    print(os.environ.get("B200_BR_KERNEL", "v2"), count, "items: blind_rotate %.3f ms, keyswitch %.3f ms" % (t["blind_rotate"], t["keyswitch"]), flush=True)
 print("checksum", int(out.to(torch.int64).sum().item()))
