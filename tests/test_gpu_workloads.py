@@ -454,3 +454,30 @@ def test_host_entry_sliced_pipeline_equals_device_path(p80):
     inplace = a.copy()
     ck.gate(GateOp.ANDYN, inplace, b, out=inplace)       # out aliases the first input exactly
     assert np.array_equal(inplace, want)
+
+
+def test_wide_circuit_level_equals_gate_batch(p80):
+    """One circuit level of 1,000 independent XOR gates and 500 MUX gates (descriptor form of the kernels: 2,000
+    rotations = two whole six-group waves plus a narrower tail launch) gives the words of the plain gate batches."""
+    import torch
+    from eoc_tfhe_b200 import GateOp
+    rk, ck = p80
+    rng = np.random.default_rng(12)
+    m = 1000
+    pool = rk.encrypt_bits(np.array([0, 1], dtype=np.int32))
+    bits = rng.integers(0, 2, size=(3, m)).astype(np.int32)
+    x, y, z = (pool[bits[i]].copy() for i in range(3))
+    for i, v in enumerate((x, y, z)):
+        v[:, rk.n] += rng.integers(-(1 << 18), 1 << 18, size=m, dtype=np.int64).astype(np.int32)
+    # wires: [0,m) x, [m,2m) y, [2m,3m) z, then outputs
+    gates = [(int(GateOp.XOR), 3 * m + i, i, m + i, -1) for i in range(m)]
+    gates += [(int(GateOp.MUX), 4 * m + i, i, m + i, 2 * m + i) for i in range(m // 2)]
+    gates = np.asarray(gates, dtype=np.int32)
+    wires = np.zeros((4 * m + m // 2, rk.n + 1), dtype=np.int32)
+    wires[:m], wires[m:2 * m], wires[2 * m:3 * m] = x, y, z
+    levels = ck.run_circuit(gates, wires)
+    assert levels == 1
+    tx, ty, tz = (torch.from_numpy(v).cuda() for v in (x, y, z))
+    assert np.array_equal(wires[3 * m:4 * m], ck.gate(GateOp.XOR, tx, ty).cpu().numpy())
+    assert np.array_equal(wires[4 * m:], ck.gate(GateOp.MUX, tx[:m // 2], ty[:m // 2], tz[:m // 2]).cpu().numpy())
+    assert np.array_equal(rk.decrypt_bits(wires[3 * m:4 * m]), bits[0] ^ bits[1])
