@@ -24,9 +24,9 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --cs
 # DRAM traffic of the two hot kernels at the bench's own launch size (65,536 gates)
 timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum,launch__grid_size --clock-control none \
     -k regex:'k_blind_rotate|k_keyswitch' -s 2 -c 2 -f -o $OUT/${TAG}_traffic python bench.py --steps 1 --warmup 1 --no-cpu-baseline > $OUT/${TAG}_ncu3.log 2>&1
-# full capture of one launch of each hot kernel (9472 gates = 16 blind-rotation waves, one key-switch wave)
-timeout 300 python scratch/prof_one.py 9472 > $OUT/${TAG}_prof_plain.log 2>&1 &&
+# full capture of one launch of each hot kernel (8880 gates = 10 whole waves of the six-group blind rotation (one launch), one key-switch wave)
+timeout 300 python scratch/prof_one.py 8880 > $OUT/${TAG}_prof_plain.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_blind_rotate|k_keyswitch' -s 2 -c 2 \
-    -f -o $OUT/${TAG}_prof python scratch/prof_one.py 9472 > $OUT/${TAG}_ncu2.log 2>&1
+    -f -o $OUT/${TAG}_prof python scratch/prof_one.py 8880 > $OUT/${TAG}_ncu2.log 2>&1
 tail -3 $OUT/${TAG}_ncu2.log
 ls -la $OUT | tail -20
