@@ -12,7 +12,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <dlfcn.h>
 #include <map>
+#include <new>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -65,9 +67,12 @@ extern "C" int b200_set_device(int device) {
 extern "C" int64_t b200_launch_count(void) { return launch_count(); }
 extern "C" int b200_set_blind_rotate_kernel(int variant) {
     if (variant < 0 || variant > 8) return b200_fail("blind-rotation kernel variant must be 0..8");
+    if (variant != 0 && !experiments_built())
+        return b200_fail("blind-rotation variants 1..8 are round-1 experiments: rebuild with -DB200_EXPERIMENTS");
     set_blind_rotate_variant(variant);
     return 0;
 }
+extern "C" int b200_experiments_built(void) { return experiments_built() ? 1 : 0; }
 
 extern "C" int b200_set_keyswitch_kernel(int variant) {
     if (variant < 0 || variant > 2) return b200_fail("key-switch kernel variant must be 0 (auto), 1 (gather) or 2 (streaming)");
@@ -92,17 +97,19 @@ static int key_alloc(const b200_params *p, b200_key **out) {
     *out = nullptr;
     if (check_params(p)) return 1;
     if (b200_device_count() <= 0) return fail("no CUDA device: libb200tfhe has no CPU fallback");
-    CK(cudaSetDevice(g_device));
-    b200_key *k = new b200_key();
+    B200_ON_DEVICE(g_device);
+    b200_key *k = new (std::nothrow) b200_key();
+    if (!k) return fail("out of host memory");
     DeviceKey &d = k->dk;
     d.n = p->n; d.N = p->N; d.k = p->k; d.l = p->l; d.Bgbit = p->Bgbit;
     d.ks_t = p->ks_t; d.ks_basebit = p->ks_basebit; d.ks_variance = p->ks_variance;
     d.ks_stride = (p->n + 1 + 3) & ~3;
     d.device = g_device;
     const int kpl = (d.k + 1) * d.l, base = 1 << d.ks_basebit;
-    // both evaluation-domain layouts live in one blob (one broadcast replicates the key)
+    // the evaluation-domain key is one blob (one broadcast replicates it); an experiments build appends the
+    // layout of the warp-per-ciphertext transform
     const size_t bk_elems = (size_t)d.n * kpl * (d.k + 1) * (d.N / 2);
-    d.bkfft_bytes = 2 * bk_elems * sizeof(double2);
+    d.bkfft_bytes = (experiments_built() ? 2 : 1) * bk_elems * sizeof(double2);
     d.ks_bytes = (size_t)d.N * d.k * d.ks_t * (base - 1) * d.ks_stride * sizeof(int32_t);
     cudaError_t e = cudaMalloc((void **)&d.bkfft, d.bkfft_bytes);
     if (e == cudaSuccess) d.bkfft16 = d.bkfft + bk_elems;
@@ -116,6 +123,7 @@ static int key_alloc(const b200_params *p, b200_key **out) {
     }
     for (int i = 0; i < b200_key::kRing * 3 && e == cudaSuccess; ++i) e = cudaEventCreate(&k->ring[i / 3][i % 3]);
     if (e == cudaSuccess) e = cudaEventCreate(&k->ev_start);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&k->ev_scratch, cudaEventDisableTiming);
     if (e == cudaSuccess) e = upload_twiddles();
     if (e != cudaSuccess) {
         fail_cuda("key allocation", e);
@@ -137,6 +145,7 @@ extern "C" int b200_key_create(const b200_params *p, const int32_t *bk_coefs, co
     if (key_alloc(p, out)) return 1;
     b200_key *k = *out;
     const DeviceKey &d = k->dk;
+    B200_ON_DEVICE(d.device);
     const int kpl = (d.k + 1) * d.l, base = 1 << d.ks_basebit;
     const size_t bk_ints = (size_t)d.n * kpl * (d.k + 1) * d.N;
     const size_t ks_ints = (size_t)d.N * d.k * d.ks_t * base * (d.n + 1);
@@ -169,8 +178,8 @@ extern "C" void b200_key_free(b200_key *k) {
         for (auto *m : {&g_by_cloud, &g_by_bkfft, &g_by_ks})
             for (auto it = m->begin(); it != m->end();) it = (it->second == k) ? m->erase(it) : std::next(it);
     }
-    cudaSetDevice(k->dk.device);
-    if (k->stream) cudaStreamSynchronize(k->stream);
+    DeviceGuard dev_guard(k->dk.device);
+    cudaDeviceSynchronize();            // calls enqueued on caller streams may still be using the workspaces
     if (k->dk.bkfft) cudaFree(k->dk.bkfft);
     if (k->dk.ks) cudaFree(k->dk.ks);
     for (DevBuf *b : {&k->u, &k->in0, &k->in1, &k->in2, &k->out, &k->nz, &k->desc_rot, &k->desc_ks, &k->desc_lin, &k->desc_io, &k->acc}) b->release();
@@ -180,6 +189,7 @@ extern "C" void b200_key_free(b200_key *k) {
         for (auto &e : slot)
             if (e) cudaEventDestroy(e);
     if (k->ev_start) cudaEventDestroy(k->ev_start);
+    if (k->ev_scratch) cudaEventDestroy(k->ev_scratch);
     if (k->stream) cudaStreamDestroy(k->stream);
     if (k->stream_h2d) cudaStreamDestroy(k->stream_h2d);
     if (k->stream_d2h) cudaStreamDestroy(k->stream_d2h);
@@ -207,53 +217,104 @@ extern "C" int b200_key_device_blobs(const b200_key *k, void **d_bkfft, size_t *
 }
 
 // ---- from a live libtfhe cloud key ---------------------------------------------------------------
-extern "C" int b200_cloudkey_upload(const TFheGateBootstrappingCloudKeySet *ck, b200_key **out) {
-    if (!ck || !ck->params || !ck->bk) return fail("cloud key (or its params / bk) is NULL");
-    {
-        std::lock_guard<std::mutex> g(g_cache_mu);
-        auto it = g_by_cloud.find(ck);
-        if (it != g_by_cloud.end()) {
-            if (out) *out = it->second;
-            return 0;
-        }
-    }
+// The drop-in cache is keyed by host pointers, and malloc may hand the address of a deleted key set to the next
+// one.  Two defences: (1) delete_gate_bootstrapping_cloud_keyset / delete_LweBootstrappingKeyFFT are interposed
+// below and drop the cache entry; (2) a hit is trusted only if a fingerprint of the key material (parameters and
+// a sample of bootstrapping-key and key-switch coefficients) still matches -- otherwise the device key is freed
+// and the new key uploaded.
+static uint64_t fnv1a(uint64_t h, const void *p, size_t bytes) {
+    const unsigned char *c = (const unsigned char *)p;
+    for (size_t i = 0; i < bytes; ++i) { h ^= c[i]; h *= 1099511628211ull; }
+    return h;
+}
+static uint64_t cloudkey_fingerprint(const TFheGateBootstrappingCloudKeySet *ck) {
     const TFheGateBootstrappingParameterSet *ps = ck->params;
     const TGswParams *gp = ps->tgsw_params;
     const TLweParams *tp = gp->tlwe_params;
     const LweKeySwitchKey *ks = (ck->bkFFT && ck->bkFFT->ks) ? ck->bkFFT->ks : ck->bk->ks;
-    if (!ks) return fail("cloud key has no key-switch key");
-    b200_params p;
-    p.n = ps->in_out_params->n; p.N = tp->N; p.k = tp->k; p.l = gp->l; p.Bgbit = gp->Bgbit;
-    p.ks_t = ps->ks_t; p.ks_basebit = ps->ks_basebit;
-    if (check_params(&p)) return 1;
-    if (ks->n != p.N * p.k || ks->t != p.ks_t || ks->basebit != p.ks_basebit) return fail("key-switch key shape mismatch");
-    const int kpl = (p.k + 1) * p.l, base = 1 << p.ks_basebit, n1 = p.n + 1;
-    p.ks_variance = ks->ks[0][0][1].current_variance;
-    std::vector<int32_t> bk((size_t)p.n * kpl * (p.k + 1) * p.N), rows((size_t)ks->n * p.ks_t * base * n1);
-    for (int i = 0; i < p.n; ++i)
-        for (int r = 0; r < kpl; ++r)
-            for (int c = 0; c <= p.k; ++c)
-                std::memcpy(&bk[(((size_t)i * kpl + r) * (p.k + 1) + c) * p.N], ck->bk->bk[i].all_sample[r].a[c].coefsT,
-                            p.N * sizeof(int32_t));
-    for (int i = 0; i < ks->n; ++i)
-        for (int j = 0; j < p.ks_t; ++j)
-            for (int h = 0; h < base; ++h) {
-                int32_t *dst = &rows[(((size_t)i * p.ks_t + j) * base + h) * n1];
-                const LweSample &s = ks->ks[i][j][h];
-                std::memcpy(dst, s.a, p.n * sizeof(int32_t));
-                dst[p.n] = s.b;
+    const int32_t shape[7] = {ps->in_out_params->n, tp->N, tp->k, gp->l, gp->Bgbit, ps->ks_t, ps->ks_basebit};
+    uint64_t h = fnv1a(14695981039346656037ull, shape, sizeof shape);
+    const int n = shape[0], N = shape[1], kpl = (shape[2] + 1) * shape[3];
+    if (n > 0 && N >= 16 && kpl > 0 && ck->bk->bk) {
+        const int words = 16;
+        for (int i : {0, n / 2, n - 1})
+            for (int r : {0, kpl - 1}) {
+                const TLweSample &row = ck->bk->bk[i].all_sample[r];
+                h = fnv1a(h, row.a[0].coefsT, words * sizeof(int32_t));
+                h = fnv1a(h, row.a[shape[2]].coefsT + N - words, words * sizeof(int32_t));
             }
-    b200_key *k = nullptr;
-    if (b200_key_create(&p, bk.data(), rows.data(), &k)) return 1;
-    {
-        std::lock_guard<std::mutex> g(g_cache_mu);
-        g_by_cloud[ck] = k;
-        if (ck->bkFFT) g_by_bkfft[ck->bkFFT] = k;
-        g_by_ks[ks] = k;
-        if (ck->bk->ks) g_by_ks[ck->bk->ks] = k;
     }
-    if (out) *out = k;
-    return 0;
+    if (ks && ks->ks && ks->n > 0 && ks->t > 0 && n > 0) {
+        const int base = 1 << ks->basebit, w = std::min(8, n);
+        for (int i : {0, ks->n - 1}) {
+            const LweSample &a = ks->ks[i][0][1], &b = ks->ks[i][ks->t - 1][base - 1];
+            h = fnv1a(h, a.a, w * sizeof(int32_t));
+            h = fnv1a(h, &a.b, sizeof a.b);
+            h = fnv1a(h, b.a + (n - w), w * sizeof(int32_t));
+            h = fnv1a(h, &b.b, sizeof b.b);
+        }
+    }
+    return h ? h : 1;
+}
+
+extern "C" int b200_cloudkey_upload(const TFheGateBootstrappingCloudKeySet *ck, b200_key **out) {
+    return b200_guarded([&]() -> int {
+        if (!ck || !ck->params || !ck->bk) return fail("cloud key (or its params / bk) is NULL");
+        const uint64_t fp = cloudkey_fingerprint(ck);
+        {
+            b200_key *stale = nullptr;
+            {
+                std::lock_guard<std::mutex> g(g_cache_mu);
+                auto it = g_by_cloud.find(ck);
+                if (it != g_by_cloud.end()) {
+                    if (it->second->fingerprint == fp) {
+                        if (out) *out = it->second;
+                        return 0;
+                    }
+                    stale = it->second;   // same address, different key: the old key set was deleted behind our back
+                }
+            }
+            if (stale) b200_key_free(stale);
+        }
+        const TFheGateBootstrappingParameterSet *ps = ck->params;
+        const TGswParams *gp = ps->tgsw_params;
+        const TLweParams *tp = gp->tlwe_params;
+        const LweKeySwitchKey *ks = (ck->bkFFT && ck->bkFFT->ks) ? ck->bkFFT->ks : ck->bk->ks;
+        if (!ks) return fail("cloud key has no key-switch key");
+        b200_params p;
+        p.n = ps->in_out_params->n; p.N = tp->N; p.k = tp->k; p.l = gp->l; p.Bgbit = gp->Bgbit;
+        p.ks_t = ps->ks_t; p.ks_basebit = ps->ks_basebit;
+        if (check_params(&p)) return 1;
+        if (ks->n != p.N * p.k || ks->t != p.ks_t || ks->basebit != p.ks_basebit) return fail("key-switch key shape mismatch");
+        const int kpl = (p.k + 1) * p.l, base = 1 << p.ks_basebit, n1 = p.n + 1;
+        p.ks_variance = ks->ks[0][0][1].current_variance;
+        std::vector<int32_t> bk((size_t)p.n * kpl * (p.k + 1) * p.N), rows((size_t)ks->n * p.ks_t * base * n1);
+        for (int i = 0; i < p.n; ++i)
+            for (int r = 0; r < kpl; ++r)
+                for (int c = 0; c <= p.k; ++c)
+                    std::memcpy(&bk[(((size_t)i * kpl + r) * (p.k + 1) + c) * p.N], ck->bk->bk[i].all_sample[r].a[c].coefsT,
+                                p.N * sizeof(int32_t));
+        for (int i = 0; i < ks->n; ++i)
+            for (int j = 0; j < p.ks_t; ++j)
+                for (int h = 0; h < base; ++h) {
+                    int32_t *dst = &rows[(((size_t)i * p.ks_t + j) * base + h) * n1];
+                    const LweSample &s = ks->ks[i][j][h];
+                    std::memcpy(dst, s.a, p.n * sizeof(int32_t));
+                    dst[p.n] = s.b;
+                }
+        b200_key *k = nullptr;
+        if (b200_key_create(&p, bk.data(), rows.data(), &k)) return 1;
+        {
+            std::lock_guard<std::mutex> g(g_cache_mu);
+            k->fingerprint = fp;
+            g_by_cloud[ck] = k;
+            if (ck->bkFFT) g_by_bkfft[ck->bkFFT] = k;
+            g_by_ks[ks] = k;
+            if (ck->bk->ks) g_by_ks[ck->bk->ks] = k;
+        }
+        if (out) *out = k;
+        return 0;
+    });
 }
 
 extern "C" void b200_cloudkey_forget(const TFheGateBootstrappingCloudKeySet *ck) {
@@ -265,6 +326,31 @@ extern "C" void b200_cloudkey_forget(const TFheGateBootstrappingCloudKeySet *ck)
         k = it->second;
     }
     b200_key_free(k);
+}
+
+// libtfhe's destructors, interposed (this library is linked / preloaded BEFORE libtfhe):
+// forget the device key, then run libtfhe's own function (the next definition in link order).
+extern "C" void delete_gate_bootstrapping_cloud_keyset(TFheGateBootstrappingCloudKeySet *keyset) {
+    using fn_t = void (*)(TFheGateBootstrappingCloudKeySet *);
+    static fn_t next = (fn_t)dlsym(RTLD_NEXT, "delete_gate_bootstrapping_cloud_keyset");
+    if (keyset) b200_cloudkey_forget(keyset);
+    if (next) next(keyset);
+    else std::fprintf(stderr, "libb200tfhe: delete_gate_bootstrapping_cloud_keyset: libtfhe's definition not found after this library; host key set leaked\n");
+}
+extern "C" void delete_LweBootstrappingKeyFFT(LweBootstrappingKeyFFT *obj) {
+    using fn_t = void (*)(LweBootstrappingKeyFFT *);
+    static fn_t next = (fn_t)dlsym(RTLD_NEXT, "delete_LweBootstrappingKeyFFT");
+    if (obj) {
+        b200_key *k = nullptr;
+        {
+            std::lock_guard<std::mutex> g(g_cache_mu);
+            auto it = g_by_bkfft.find(obj);
+            if (it != g_by_bkfft.end()) k = it->second;
+        }
+        if (k) b200_key_free(k);
+    }
+    if (next) next(obj);
+    else std::fprintf(stderr, "libb200tfhe: delete_LweBootstrappingKeyFFT: libtfhe's definition not found after this library; host key leaked\n");
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -291,6 +377,7 @@ static int enqueue_gates(b200_key *k, int op, int32_t *d_out, const int32_t *d_a
     const int per = op == B200_MUX ? 2 : 1;
     const int64_t chunk_gates = kChunkItems / per;
     if (k->u.ensure((size_t)std::min<int64_t>(count, chunk_gates) * per * (d.N + 1) * sizeof(int32_t))) return 1;
+    if (k->scratch_begin(s)) return 1;
     for (int64_t g0 = 0; g0 < count; g0 += chunk_gates) {
         const int64_t g = std::min(chunk_gates, count - g0);
         BlindRotateArgs br{};
@@ -318,7 +405,7 @@ static int enqueue_gates(b200_key *k, int op, int32_t *d_out, const int32_t *d_a
             k->ring_head++;
         }
     }
-    return 0;
+    return k->scratch_end(s);
 }
 
 extern "C" int b200_gate_batch_dev(b200_key *k, int op, int32_t *d_out, const int32_t *d_a, const int32_t *d_b,
@@ -329,7 +416,7 @@ extern "C" int b200_gate_batch_dev(b200_key *k, int op, int32_t *d_out, const in
     if (count == 0) return 0;
     if (!d_out) return fail("d_out is NULL");
     std::lock_guard<std::mutex> g(k->mu);
-    CK(cudaSetDevice(k->dk.device));
+    B200_ON_DEVICE(k->dk.device);
     k->timing_pending = true;
     return enqueue_gates(k, op, d_out, d_a, d_b, d_c, count, nullptr, (cudaStream_t)stream, true);
 }
@@ -339,7 +426,7 @@ static int gate_batch_host_locked(b200_key *k, int op, int32_t *out, const int32
     const DeviceKey &d = k->dk;
     const size_t bytes = (size_t)count * (d.n + 1) * sizeof(int32_t);
     cudaStream_t s = k->stream;
-    CK(cudaSetDevice(d.device));
+    B200_ON_DEVICE(d.device);
     const bool need_a = !(op == B200_CONST0 || op == B200_CONST1);
     const bool need_b = !op_is_linear(op);
     const bool need_c = op == B200_MUX;
@@ -360,17 +447,23 @@ static int gate_batch_host_locked(b200_key *k, int op, int32_t *out, const int32
         const char *i0 = (const char *)in, *o0 = (const char *)out;
         return i0 < o0 + bytes && o0 < i0 + bytes;
     };
-    if (!op_is_linear(op) && !nonzero && count >= 2 * kSliceSmall && !shifted_overlap(a) && !shifted_overlap(b) &&
+    if (!op_is_linear(op) && count >= 2 * kSliceSmall && !shifted_overlap(a) && !shifted_overlap(b) &&
         !shifted_overlap(need_c ? c : nullptr)) {
         const int n1 = d.n + 1;
+        int32_t *d_nz_all = nullptr;      // per-gate count of non-zero key-switch digits (-> current_variance)
+        if (nonzero) {
+            if (k->nz.ensure((size_t)count * sizeof(int32_t))) return 1;
+            d_nz_all = (int32_t *)k->nz.p;
+            CK(cudaMemsetAsync(d_nz_all, 0, (size_t)count * sizeof(int32_t), s));
+        }
         int64_t slice = std::max<int64_t>(1, (count / 4 + kSliceQuantum / 2) / kSliceQuantum) * kSliceQuantum;   // about a quarter, at least one quantum
         while ((count + slice - 1) / slice > b200_key::kSlices) slice += kSliceQuantum;
         if (k->in0.ensure(bytes) || k->in1.ensure(bytes) || (need_c && k->in2.ensure(bytes))) return 1;
         CK(cudaEventRecord(k->ev_up[0], s));                 // order after earlier work on the key's stream
         CK(cudaStreamWaitEvent(k->stream_h2d, k->ev_up[0], 0));
         CK(cudaStreamWaitEvent(k->stream_d2h, k->ev_up[0], 0));
-        int i = 0;
-        for (int64_t g0 = 0; g0 < count; g0 += slice, ++i) {
+        // one slice: upload on the copy stream, kernels on the key's stream, download on the third stream
+        auto run_slice = [&](int i, int64_t g0) -> int {
             const int64_t g = std::min(slice, count - g0);
             const size_t off = (size_t)g0 * n1, sb = (size_t)g * n1 * sizeof(int32_t);
             CK(cudaMemcpyAsync((int32_t *)k->in0.p + off, a + off, sb, cudaMemcpyHostToDevice, k->stream_h2d));
@@ -379,14 +472,24 @@ static int gate_batch_host_locked(b200_key *k, int op, int32_t *out, const int32
             CK(cudaEventRecord(k->ev_up[i], k->stream_h2d));
             CK(cudaStreamWaitEvent(s, k->ev_up[i], 0));
             if (enqueue_gates(k, op, (int32_t *)k->out.p + off, (const int32_t *)k->in0.p + off, (const int32_t *)k->in1.p + off,
-                              need_c ? (const int32_t *)k->in2.p + off : nullptr, g, nullptr, s, i == 0))
+                              need_c ? (const int32_t *)k->in2.p + off : nullptr, g, d_nz_all ? d_nz_all + g0 : nullptr, s, i == 0))
                 return 1;
             CK(cudaEventRecord(k->ev_done[i], s));
             CK(cudaStreamWaitEvent(k->stream_d2h, k->ev_done[i], 0));
             CK(cudaMemcpyAsync(out + off, (int32_t *)k->out.p + off, sb, cudaMemcpyDeviceToHost, k->stream_d2h));
-        }
-        CK(cudaStreamSynchronize(k->stream_d2h));
-        CK(cudaStreamSynchronize(s));
+            if (d_nz_all) CK(cudaMemcpyAsync(nonzero + g0, d_nz_all + g0, (size_t)g * sizeof(int32_t), cudaMemcpyDeviceToHost, k->stream_d2h));
+            return 0;
+        };
+        int i = 0, rc = 0;
+        for (int64_t g0 = 0; g0 < count && !rc; g0 += slice, ++i) rc = run_slice(i, g0);
+        // Also on failure: copies that read the caller's a / b / c and write the caller's out may still be in
+        // flight on the copy streams; the caller may free those buffers as soon as this call returns.
+        const cudaError_t e1 = cudaStreamSynchronize(k->stream_h2d), e2 = cudaStreamSynchronize(s),
+                          e3 = cudaStreamSynchronize(k->stream_d2h);
+        if (rc) return 1;
+        if (e1 != cudaSuccess) return fail_cuda("host batch pipeline (upload stream)", e1);
+        if (e2 != cudaSuccess) return fail_cuda("host batch pipeline (kernel stream)", e2);
+        if (e3 != cudaSuccess) return fail_cuda("host batch pipeline (download stream)", e3);
         k->timing_pending = true;
         return 0;
     }
@@ -423,7 +526,7 @@ extern "C" int b200_gate_batch_host(b200_key *k, int op, int32_t *out, const int
 extern "C" int b200_last_timing_ms(b200_key *k, float out_ms[3]) {
     if (!k || !out_ms) return fail("NULL argument");
     std::lock_guard<std::mutex> g(k->mu);
-    CK(cudaSetDevice(k->dk.device));
+    B200_ON_DEVICE(k->dk.device);
     if (k->timing_pending && k->ring_head > 0) {
         cudaEvent_t *ev = k->ring[(k->ring_head - 1) % b200_key::kRing];
         CK(cudaEventSynchronize(ev[2]));
@@ -441,7 +544,7 @@ extern "C" int b200_last_timing_ms(b200_key *k, float out_ms[3]) {
 extern "C" int b200_timing_drain(b200_key *k, double sum_ms[2], int32_t *calls) {
     if (!k || !sum_ms || !calls) return fail("NULL argument");
     std::lock_guard<std::mutex> g(k->mu);
-    CK(cudaSetDevice(k->dk.device));
+    B200_ON_DEVICE(k->dk.device);
     sum_ms[0] = sum_ms[1] = 0;
     *calls = 0;
     const int64_t begin = std::max(k->ring_drained, k->ring_head - b200_key::kRing);
@@ -462,7 +565,7 @@ extern "C" int b200_timing_drain(b200_key *k, double sum_ms[2], int32_t *calls) 
 extern "C" int b200_fp64_peak_tflops(int device, double *tflops) {
     if (!tflops) return fail("NULL argument");
     if (b200_device_count() <= 0) return fail("no CUDA device");
-    CK(cudaSetDevice(device));
+    B200_ON_DEVICE(device);
     CK(measure_fp64_peak(tflops));
     return 0;
 }
@@ -511,12 +614,14 @@ static b200_key *key_for_cloud(const TFheGateBootstrappingCloudKeySet *ck) {
 
 extern "C" int bootsGate_batch(int op, LweSample *const *out, const LweSample *const *a, const LweSample *const *b,
                                const LweSample *const *c, int32_t count, const TFheGateBootstrappingCloudKeySet *bk) {
-    if (!op_valid(op)) return fail("invalid gate op");
-    if (count < 0) return fail("negative count");
-    if (count == 0) return 0;
-    b200_key *k = key_for_cloud(bk);
-    if (!k) return 1;
-    return gate_batch_samples(k, op, out, a, b, c, count);
+    return b200_guarded([&]() -> int {
+        if (!op_valid(op)) return fail("invalid gate op");
+        if (count < 0) return fail("negative count");
+        if (count == 0) return 0;
+        b200_key *k = key_for_cloud(bk);
+        if (!k) return 1;
+        return gate_batch_samples(k, op, out, a, b, c, count);
+    });
 }
 
 // ---- libtfhe drop-in gates (batch of one: the latency path) ----------------------------------------
@@ -571,9 +676,10 @@ extern "C" void bootsCONSTANT(LweSample *r, int32_t value, const TFheGateBootstr
 static int woks_locked(b200_key *k, int32_t *u, const int32_t *x, int32_t mu, int64_t count) {
     const DeviceKey &d = k->dk;
     cudaStream_t s = k->stream;
-    CK(cudaSetDevice(d.device));
+    B200_ON_DEVICE(d.device);
     const size_t in_bytes = (size_t)count * (d.n + 1) * 4, u_bytes = (size_t)count * (d.N + 1) * 4;
     if (k->in0.ensure(in_bytes) || k->u.ensure(u_bytes)) return 1;
+    if (k->scratch_begin(s)) return 1;
     CK(cudaMemcpyAsync(k->in0.p, x, in_bytes, cudaMemcpyHostToDevice, s));
     BlindRotateArgs br{};
     br.in0 = (const int32_t *)k->in0.p;
@@ -601,7 +707,7 @@ extern "C" int b200_keyswitch_dev(b200_key *k, int32_t *d_out, const int32_t *d_
     if (count == 0) return 0;
     if (!d_out || !d_u) return fail("NULL device pointer");
     std::lock_guard<std::mutex> g(k->mu);
-    CK(cudaSetDevice(k->dk.device));
+    B200_ON_DEVICE(k->dk.device);
     KeySwitchArgs ks{};
     ks.u = d_u;
     ks.out = d_out;
@@ -613,9 +719,10 @@ extern "C" int b200_keyswitch_dev(b200_key *k, int32_t *d_out, const int32_t *d_
 static int keyswitch_locked(b200_key *k, int32_t *out, const int32_t *u, int32_t *nonzero, int64_t count) {
     const DeviceKey &d = k->dk;
     cudaStream_t s = k->stream;
-    CK(cudaSetDevice(d.device));
+    B200_ON_DEVICE(d.device);
     const size_t out_bytes = (size_t)count * (d.n + 1) * 4, u_bytes = (size_t)count * (d.N + 1) * 4;
     if (k->u.ensure(u_bytes) || k->out.ensure(out_bytes) || k->nz.ensure((size_t)count * 4)) return 1;
+    if (k->scratch_begin(s)) return 1;
     CK(cudaMemcpyAsync(k->u.p, u, u_bytes, cudaMemcpyHostToDevice, s));
     CK(cudaMemsetAsync(k->nz.p, 0, (size_t)count * 4, s));
     KeySwitchArgs ks{};
@@ -648,7 +755,7 @@ static int cmux_host(b200_key *k, int32_t *acc, int32_t bk_index, int32_t barai,
     std::lock_guard<std::mutex> g(k->mu);
     const DeviceKey &d = k->dk;
     cudaStream_t s = k->stream;
-    CK(cudaSetDevice(d.device));
+    B200_ON_DEVICE(d.device);
     const size_t bytes = (size_t)count * (d.k + 1) * d.N * 4;
     if (k->acc.ensure(bytes)) return 1;
     CK(cudaMemcpyAsync(k->acc.p, acc, bytes, cudaMemcpyHostToDevice, s));

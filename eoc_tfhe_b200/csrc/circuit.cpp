@@ -18,44 +18,46 @@ static bool lin_op(int op) { return op == B200_NOT || op == B200_COPY || op == B
 
 extern "C" int b200_circuit_levelize(const int32_t *gates, int64_t num_gates, int64_t num_wires, int32_t *gate_level,
                                      int32_t *num_levels) {
-    if (!gates || num_gates < 0 || num_wires <= 0) return b200_fail("bad netlist arguments");
-    std::vector<int32_t> ready(num_wires, 0);
-    std::vector<uint8_t> written(num_wires, 0);
-    int32_t maxl = 0;
-    for (int64_t g = 0; g < num_gates; ++g) {
-        const int32_t *G = gates + g * 5;
-        const int op = G[0];
-        if (op < 0 || op >= B200_GATE_OP_COUNT) return b200_fail("netlist: invalid op");
-        const int nin = lin_op(op) ? ((op == B200_NOT || op == B200_COPY) ? 1 : 0) : (op == B200_MUX ? 3 : 2);
-        if (G[1] < 0 || G[1] >= num_wires) return b200_fail("netlist: output wire out of range");
-        if (written[G[1]]) return b200_fail("netlist: wire written twice");
-        int32_t lvl = 0;
-        for (int i = 0; i < nin; ++i) {
-            const int32_t w = G[2 + i];
-            if (w < 0 || w >= num_wires) return b200_fail("netlist: input wire out of range");
-            if (w == G[1]) return b200_fail("netlist: gate reads its own output");
-            lvl = std::max(lvl, ready[w]);
+    return b200_guarded([&]() -> int {
+        if (!gates || num_gates < 0 || num_wires <= 0) return b200_fail("bad netlist arguments");
+        std::vector<int32_t> ready(num_wires, 0);
+        std::vector<uint8_t> written(num_wires, 0);
+        int32_t maxl = 0;
+        for (int64_t g = 0; g < num_gates; ++g) {
+            const int32_t *G = gates + g * 5;
+            const int op = G[0];
+            if (op < 0 || op >= B200_GATE_OP_COUNT) return b200_fail("netlist: invalid op");
+            const int nin = lin_op(op) ? ((op == B200_NOT || op == B200_COPY) ? 1 : 0) : (op == B200_MUX ? 3 : 2);
+            if (G[1] < 0 || G[1] >= num_wires) return b200_fail("netlist: output wire out of range");
+            if (written[G[1]]) return b200_fail("netlist: wire written twice");
+            int32_t lvl = 0;
+            for (int i = 0; i < nin; ++i) {
+                const int32_t w = G[2 + i];
+                if (w < 0 || w >= num_wires) return b200_fail("netlist: input wire out of range");
+                if (w == G[1]) return b200_fail("netlist: gate reads its own output");
+                lvl = std::max(lvl, ready[w]);
+            }
+            if (!lin_op(op)) lvl += 1;
+            ready[G[1]] = lvl;
+            written[G[1]] = 1;
+            if (gate_level) gate_level[g] = lvl;
+            maxl = std::max(maxl, lvl);
         }
-        if (!lin_op(op)) lvl += 1;
-        ready[G[1]] = lvl;
-        written[G[1]] = 1;
-        if (gate_level) gate_level[g] = lvl;
-        maxl = std::max(maxl, lvl);
-    }
-    // a gate may only read wires that are inputs or were written by an EARLIER gate
-    std::fill(written.begin(), written.end(), 0);
-    std::vector<uint8_t> is_out(num_wires, 0);
-    for (int64_t g = 0; g < num_gates; ++g) is_out[gates[g * 5 + 1]] = 1;
-    for (int64_t g = 0; g < num_gates; ++g) {
-        const int32_t *G = gates + g * 5;
-        const int op = G[0];
-        const int nin = lin_op(op) ? ((op == B200_NOT || op == B200_COPY) ? 1 : 0) : (op == B200_MUX ? 3 : 2);
-        for (int i = 0; i < nin; ++i)
-            if (is_out[G[2 + i]] && !written[G[2 + i]]) return b200_fail("netlist: not in topological order");
-        written[G[1]] = 1;
-    }
-    if (num_levels) *num_levels = maxl;
-    return 0;
+        // a gate may only read wires that are inputs or were written by an EARLIER gate
+        std::fill(written.begin(), written.end(), 0);
+        std::vector<uint8_t> is_out(num_wires, 0);
+        for (int64_t g = 0; g < num_gates; ++g) is_out[gates[g * 5 + 1]] = 1;
+        for (int64_t g = 0; g < num_gates; ++g) {
+            const int32_t *G = gates + g * 5;
+            const int op = G[0];
+            const int nin = lin_op(op) ? ((op == B200_NOT || op == B200_COPY) ? 1 : 0) : (op == B200_MUX ? 3 : 2);
+            for (int i = 0; i < nin; ++i)
+                if (is_out[G[2 + i]] && !written[G[2 + i]]) return b200_fail("netlist: not in topological order");
+            written[G[1]] = 1;
+        }
+        if (num_levels) *num_levels = maxl;
+        return 0;
+    });
 }
 
 extern "C" int b200_expand_gates(const int32_t *gates, int64_t num_gates, int32_t *rot_desc, int64_t *n_rot,
@@ -100,6 +102,7 @@ static int level_run_locked(b200_key *key, int32_t *d_wires, const int32_t *rot_
     if (key->desc_rot.ensure(n_rot * 16) || key->desc_ks.ensure(n_ks * 16) ||
         key->u.ensure((size_t)n_rot * (d.N + 1) * 4))
         return 1;
+    if (key->scratch_begin(s)) return 1;
     B200_CK(cudaMemcpyAsync(key->desc_rot.p, rot_desc, n_rot * 16, cudaMemcpyHostToDevice, s));
     B200_CK(cudaMemcpyAsync(key->desc_ks.p, ks_desc, n_ks * 16, cudaMemcpyHostToDevice, s));
     BlindRotateArgs br{};
@@ -116,7 +119,7 @@ static int level_run_locked(b200_key *key, int32_t *d_wires, const int32_t *rot_
     ks.items = n_ks;
     B200_CK(launch_keyswitch(d, ks, s));
     // descriptors were copied from pageable host memory: the copy is complete (staged) on return
-    return 0;
+    return key->scratch_end(s);
 }
 
 extern "C" int b200_level_run_dev(b200_key *key, int32_t *d_wires, const int32_t *rot_desc, int64_t n_rot,
@@ -124,7 +127,7 @@ extern "C" int b200_level_run_dev(b200_key *key, int32_t *d_wires, const int32_t
     if (!key || !key->filled) return b200_fail("key is NULL or not filled");
     if (!d_wires || !rot_desc || !ks_desc) return b200_fail("NULL argument");
     std::lock_guard<std::mutex> g(key->mu);
-    B200_CK(cudaSetDevice(key->dk.device));
+    B200_ON_DEVICE(key->dk.device);
     return level_run_locked(key, d_wires, rot_desc, n_rot, ks_desc, n_ks, (cudaStream_t)stream);
 }
 
@@ -200,27 +203,31 @@ static int circuit_run_locked(b200_key *key, const int32_t *gates, int64_t num_g
 
 extern "C" int b200_circuit_run_dev(b200_key *key, const int32_t *gates, int64_t num_gates, int32_t *d_wires,
                                     int64_t num_wires, int32_t *levels_out, void *stream) {
-    if (!key || !key->filled) return b200_fail("key is NULL or not filled");
-    if (!gates || !d_wires) return b200_fail("NULL argument");
-    std::lock_guard<std::mutex> g(key->mu);
-    B200_CK(cudaSetDevice(key->dk.device));
-    return circuit_run_locked(key, gates, num_gates, d_wires, num_wires, levels_out, (cudaStream_t)stream);
+    return b200_guarded([&]() -> int {
+        if (!key || !key->filled) return b200_fail("key is NULL or not filled");
+        if (!gates || !d_wires) return b200_fail("NULL argument");
+        std::lock_guard<std::mutex> g(key->mu);
+        B200_ON_DEVICE(key->dk.device);
+        return circuit_run_locked(key, gates, num_gates, d_wires, num_wires, levels_out, (cudaStream_t)stream);
+    });
 }
 
 extern "C" int b200_circuit_run_host(b200_key *key, const int32_t *gates, int64_t num_gates, int32_t *wires,
                                      int64_t num_wires, int32_t *levels_out) {
-    if (!key || !key->filled) return b200_fail("key is NULL or not filled");
-    if (!gates || !wires) return b200_fail("NULL argument");
-    std::lock_guard<std::mutex> g(key->mu);
-    B200_CK(cudaSetDevice(key->dk.device));
-    const size_t bytes = (size_t)num_wires * (key->dk.n + 1) * 4;
-    if (key->out.ensure(bytes)) return 1;
-    cudaStream_t s = key->stream;
-    B200_CK(cudaMemcpyAsync(key->out.p, wires, bytes, cudaMemcpyHostToDevice, s));
-    if (circuit_run_locked(key, gates, num_gates, (int32_t *)key->out.p, num_wires, levels_out, s)) return 1;
-    B200_CK(cudaMemcpyAsync(wires, key->out.p, bytes, cudaMemcpyDeviceToHost, s));
-    B200_CK(cudaStreamSynchronize(s));
-    return 0;
+    return b200_guarded([&]() -> int {
+        if (!key || !key->filled) return b200_fail("key is NULL or not filled");
+        if (!gates || !wires) return b200_fail("NULL argument");
+        std::lock_guard<std::mutex> g(key->mu);
+        B200_ON_DEVICE(key->dk.device);
+        const size_t bytes = (size_t)num_wires * (key->dk.n + 1) * 4;
+        if (key->out.ensure(bytes)) return 1;
+        cudaStream_t s = key->stream;
+        B200_CK(cudaMemcpyAsync(key->out.p, wires, bytes, cudaMemcpyHostToDevice, s));
+        if (circuit_run_locked(key, gates, num_gates, (int32_t *)key->out.p, num_wires, levels_out, s)) return 1;
+        B200_CK(cudaMemcpyAsync(wires, key->out.p, bytes, cudaMemcpyDeviceToHost, s));
+        B200_CK(cudaStreamSynchronize(s));
+        return 0;
+    });
 }
 
 // Packed I/O: the device pool is [num_wires | n_in staged input rows | n_out staged output rows]; inputs
@@ -230,41 +237,43 @@ extern "C" int b200_circuit_run_host_io(b200_key *key, const int32_t *gates, int
                                         const int32_t *in_wires, int64_t n_in, const int32_t *in_rows,
                                         const int32_t *out_wires, int64_t n_out, int32_t *out_rows,
                                         int32_t *levels_out) {
-    if (!key || !key->filled) return b200_fail("key is NULL or not filled");
-    if (!gates || num_wires <= 0 || n_in < 0 || n_out < 0 || (n_in && (!in_wires || !in_rows)) ||
-        (n_out && (!out_wires || !out_rows)))
-        return b200_fail("bad argument");
-    if (num_wires + n_in + n_out > 0x7fffffffLL) return b200_fail("wire pool too large");
-    std::vector<int32_t> desc((size_t)(n_in + n_out) * 4);
-    for (int64_t i = 0; i < n_in; ++i) {
-        if (in_wires[i] < 0 || in_wires[i] >= num_wires) return b200_fail("input wire out of range");
-        int32_t *d = &desc[(size_t)i * 4];
-        d[0] = B200_COPY; d[1] = in_wires[i]; d[2] = (int32_t)(num_wires + i); d[3] = 0;
-    }
-    for (int64_t i = 0; i < n_out; ++i) {
-        if (out_wires[i] < 0 || out_wires[i] >= num_wires) return b200_fail("output wire out of range");
-        int32_t *d = &desc[(size_t)(n_in + i) * 4];
-        d[0] = B200_COPY; d[1] = (int32_t)(num_wires + n_in + i); d[2] = out_wires[i]; d[3] = 0;
-    }
-    std::lock_guard<std::mutex> g(key->mu);
-    B200_CK(cudaSetDevice(key->dk.device));
-    const size_t row = (size_t)(key->dk.n + 1) * 4;
-    if (key->out.ensure((size_t)(num_wires + n_in + n_out) * row)) return 1;
-    if (key->desc_io.ensure(desc.size() * 4 + 16)) return 1;
-    cudaStream_t s = key->stream;
-    int32_t *pool = (int32_t *)key->out.p;
-    int32_t *d_desc = (int32_t *)key->desc_io.p;
-    B200_CK(cudaMemsetAsync(pool, 0, (size_t)num_wires * row, s));
-    if (!desc.empty()) B200_CK(cudaMemcpyAsync(d_desc, desc.data(), desc.size() * 4, cudaMemcpyHostToDevice, s));
-    if (n_in) {
-        B200_CK(cudaMemcpyAsync((char *)pool + (size_t)num_wires * row, in_rows, (size_t)n_in * row, cudaMemcpyHostToDevice, s));
-        B200_CK(b200::launch_linear_desc(key->dk, pool, d_desc, n_in, s));
-    }
-    if (circuit_run_locked(key, gates, num_gates, pool, num_wires, levels_out, s)) return 1;
-    if (n_out) {
-        B200_CK(b200::launch_linear_desc(key->dk, pool, d_desc + (size_t)n_in * 4, n_out, s));
-        B200_CK(cudaMemcpyAsync(out_rows, (char *)pool + (size_t)(num_wires + n_in) * row, (size_t)n_out * row, cudaMemcpyDeviceToHost, s));
-    }
-    B200_CK(cudaStreamSynchronize(s));
-    return 0;
+    return b200_guarded([&]() -> int {
+        if (!key || !key->filled) return b200_fail("key is NULL or not filled");
+        if (!gates || num_wires <= 0 || n_in < 0 || n_out < 0 || (n_in && (!in_wires || !in_rows)) ||
+            (n_out && (!out_wires || !out_rows)))
+            return b200_fail("bad argument");
+        if (num_wires + n_in + n_out > 0x7fffffffLL) return b200_fail("wire pool too large");
+        std::vector<int32_t> desc((size_t)(n_in + n_out) * 4);
+        for (int64_t i = 0; i < n_in; ++i) {
+            if (in_wires[i] < 0 || in_wires[i] >= num_wires) return b200_fail("input wire out of range");
+            int32_t *d = &desc[(size_t)i * 4];
+            d[0] = B200_COPY; d[1] = in_wires[i]; d[2] = (int32_t)(num_wires + i); d[3] = 0;
+        }
+        for (int64_t i = 0; i < n_out; ++i) {
+            if (out_wires[i] < 0 || out_wires[i] >= num_wires) return b200_fail("output wire out of range");
+            int32_t *d = &desc[(size_t)(n_in + i) * 4];
+            d[0] = B200_COPY; d[1] = (int32_t)(num_wires + n_in + i); d[2] = out_wires[i]; d[3] = 0;
+        }
+        std::lock_guard<std::mutex> g(key->mu);
+        B200_ON_DEVICE(key->dk.device);
+        const size_t row = (size_t)(key->dk.n + 1) * 4;
+        if (key->out.ensure((size_t)(num_wires + n_in + n_out) * row)) return 1;
+        if (key->desc_io.ensure(desc.size() * 4 + 16)) return 1;
+        cudaStream_t s = key->stream;
+        int32_t *pool = (int32_t *)key->out.p;
+        int32_t *d_desc = (int32_t *)key->desc_io.p;
+        B200_CK(cudaMemsetAsync(pool, 0, (size_t)num_wires * row, s));
+        if (!desc.empty()) B200_CK(cudaMemcpyAsync(d_desc, desc.data(), desc.size() * 4, cudaMemcpyHostToDevice, s));
+        if (n_in) {
+            B200_CK(cudaMemcpyAsync((char *)pool + (size_t)num_wires * row, in_rows, (size_t)n_in * row, cudaMemcpyHostToDevice, s));
+            B200_CK(b200::launch_linear_desc(key->dk, pool, d_desc, n_in, s));
+        }
+        if (circuit_run_locked(key, gates, num_gates, pool, num_wires, levels_out, s)) return 1;
+        if (n_out) {
+            B200_CK(b200::launch_linear_desc(key->dk, pool, d_desc + (size_t)n_in * 4, n_out, s));
+            B200_CK(cudaMemcpyAsync(out_rows, (char *)pool + (size_t)(num_wires + n_in) * row, (size_t)n_out * row, cudaMemcpyDeviceToHost, s));
+        }
+        B200_CK(cudaStreamSynchronize(s));
+        return 0;
+    });
 }

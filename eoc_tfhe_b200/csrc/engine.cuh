@@ -71,6 +71,7 @@ cudaError_t launch_linear_desc(const DeviceKey &key, int32_t *pool, const int32_
                                int64_t items, cudaStream_t s);
 int64_t launch_count();
 void set_blind_rotate_variant(int v);  // 0: 64 threads per ciphertext, 1: warp per ciphertext (TMEM)
+bool experiments_built();              // compiled with -DB200_EXPERIMENTS (round-1 blind-rotation variants 1..8)
 void set_keyswitch_variant(int v);     // 0: chosen by batch size, 1: gather kernel, 2: table-streaming kernel
 cudaError_t measure_fp64_peak(double *tflops);
 

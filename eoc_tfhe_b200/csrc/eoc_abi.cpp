@@ -146,39 +146,41 @@ void ripple_netlist(int nb_bits, int subtract, std::vector<int32_t> &gates, int3
 
 extern "C" int b200_add_bits_host(b200_key *key, int32_t *sum, const int32_t *x, const int32_t *y, int32_t nb_bits,
                                   int64_t count, int subtract) {
-    if (!key) return b200_fail("key is NULL");
-    if (!sum || !x || !y || nb_bits <= 0 || nb_bits > 4096 || count < 0) return b200_fail("bad argument");
-    if (count == 0) return 0;
-    b200_params P;
-    if (b200_key_params(key, &P)) return 1;
-    const size_t n1 = (size_t)P.n + 1;
-    std::vector<int32_t> one, outw;
-    int32_t nw = 0;
-    ripple_netlist(nb_bits, subtract != 0, one, nw, outw);
-    const int64_t per = (int64_t)one.size() / 5;
-    if ((int64_t)nw * count > 0x7fffffffLL) return b200_fail("too many operand pairs for one call");
-    // `count` independent instances over one pool, instance-major, so that a level holds the gates of
-    // that depth of every operand pair
-    std::vector<int32_t> gates((size_t)per * 5 * count);
-    for (int64_t c = 0; c < count; ++c)
-        for (int64_t g = 0; g < per; ++g) {
-            int32_t *row = &gates[((size_t)c * per + g) * 5];
-            row[0] = one[g * 5];
-            for (int f = 1; f < 5; ++f) row[f] = one[g * 5 + f] < 0 ? -1 : (int32_t)(one[g * 5 + f] + c * nw);
+    return b200_guarded([&]() -> int {
+        if (!key) return b200_fail("key is NULL");
+        if (!sum || !x || !y || nb_bits <= 0 || nb_bits > 4096 || count < 0) return b200_fail("bad argument");
+        if (count == 0) return 0;
+        b200_params P;
+        if (b200_key_params(key, &P)) return 1;
+        const size_t n1 = (size_t)P.n + 1;
+        std::vector<int32_t> one, outw;
+        int32_t nw = 0;
+        ripple_netlist(nb_bits, subtract != 0, one, nw, outw);
+        const int64_t per = (int64_t)one.size() / 5;
+        if ((int64_t)nw * count > 0x7fffffffLL) return b200_fail("too many operand pairs for one call");
+        // `count` independent instances over one pool, instance-major, so that a level holds the gates of
+        // that depth of every operand pair
+        std::vector<int32_t> gates((size_t)per * 5 * count);
+        for (int64_t c = 0; c < count; ++c)
+            for (int64_t g = 0; g < per; ++g) {
+                int32_t *row = &gates[((size_t)c * per + g) * 5];
+                row[0] = one[g * 5];
+                for (int f = 1; f < 5; ++f) row[f] = one[g * 5 + f] < 0 ? -1 : (int32_t)(one[g * 5 + f] + c * nw);
+            }
+        // packed I/O: operand rows go up as they are (x bits, then y bits, per pair), sum rows come back
+        std::vector<int32_t> in_wires((size_t)count * 2 * nb_bits), out_wires((size_t)count * (nb_bits + 1));
+        std::vector<int32_t> in_rows((size_t)count * 2 * nb_bits * n1);
+        for (int64_t c = 0; c < count; ++c) {
+            for (int i = 0; i < 2 * nb_bits; ++i) in_wires[(size_t)c * 2 * nb_bits + i] = (int32_t)(c * nw + i);
+            for (int i = 0; i <= nb_bits; ++i) out_wires[(size_t)c * (nb_bits + 1) + i] = (int32_t)(c * nw + outw[i]);
+            std::memcpy(&in_rows[(size_t)c * 2 * nb_bits * n1], x + (size_t)c * nb_bits * n1, (size_t)nb_bits * n1 * 4);
+            std::memcpy(&in_rows[((size_t)c * 2 + 1) * nb_bits * n1], y + (size_t)c * nb_bits * n1, (size_t)nb_bits * n1 * 4);
         }
-    // packed I/O: operand rows go up as they are (x bits, then y bits, per pair), sum rows come back
-    std::vector<int32_t> in_wires((size_t)count * 2 * nb_bits), out_wires((size_t)count * (nb_bits + 1));
-    std::vector<int32_t> in_rows((size_t)count * 2 * nb_bits * n1);
-    for (int64_t c = 0; c < count; ++c) {
-        for (int i = 0; i < 2 * nb_bits; ++i) in_wires[(size_t)c * 2 * nb_bits + i] = (int32_t)(c * nw + i);
-        for (int i = 0; i <= nb_bits; ++i) out_wires[(size_t)c * (nb_bits + 1) + i] = (int32_t)(c * nw + outw[i]);
-        std::memcpy(&in_rows[(size_t)c * 2 * nb_bits * n1], x + (size_t)c * nb_bits * n1, (size_t)nb_bits * n1 * 4);
-        std::memcpy(&in_rows[((size_t)c * 2 + 1) * nb_bits * n1], y + (size_t)c * nb_bits * n1, (size_t)nb_bits * n1 * 4);
-    }
-    if (b200_circuit_run_host_io(key, gates.data(), per * count, (int64_t)nw * count, in_wires.data(), (int64_t)in_wires.size(),
-                                 in_rows.data(), out_wires.data(), (int64_t)out_wires.size(), sum, nullptr))
-        return 1;
-    return 0;
+        if (b200_circuit_run_host_io(key, gates.data(), per * count, (int64_t)nw * count, in_wires.data(), (int64_t)in_wires.size(),
+                                     in_rows.data(), out_wires.data(), (int64_t)out_wires.size(), sum, nullptr))
+            return 1;
+        return 0;
+    });
 }
 
 extern "C" int b200_eoc_set_key(b200_key *key) {
@@ -190,15 +192,17 @@ extern "C" int b200_eoc_set_key(b200_key *key) {
 }
 
 extern "C" int b200_eoc_set_cloud_key(const char *base64_cloud_key) {
-    if (!base64_cloud_key) return b200_fail("NULL cloud key string");
-    const std::vector<unsigned char> raw = b64_decode(base64_cloud_key);
-    b200_key *k = nullptr;
-    if (b200_key_from_cloudkey_bytes(raw.data(), raw.size(), &k)) return 1;
-    std::lock_guard<std::mutex> g(g_eval_mu);
-    if (g_eval_key && g_eval_key_owned) b200_key_free(g_eval_key);
-    g_eval_key = k;
-    g_eval_key_owned = true;
-    return 0;
+    return b200_guarded([&]() -> int {
+        if (!base64_cloud_key) return b200_fail("NULL cloud key string");
+        const std::vector<unsigned char> raw = b64_decode(base64_cloud_key);
+        b200_key *k = nullptr;
+        if (b200_key_from_cloudkey_bytes(raw.data(), raw.size(), &k)) return 1;
+        std::lock_guard<std::mutex> g(g_eval_mu);
+        if (g_eval_key && g_eval_key_owned) b200_key_free(g_eval_key);
+        g_eval_key = k;
+        g_eval_key_owned = true;
+        return 0;
+    });
 }
 
 extern "C" void b200_eoc_free(const char *s) { delete[] s; }

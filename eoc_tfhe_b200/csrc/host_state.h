@@ -2,7 +2,9 @@
 #pragma once
 #include "engine.cuh"
 
+#include <exception>
 #include <mutex>
+#include <new>
 #include <string>
 
 int b200_fail(const std::string &msg);                 // records the message, returns 1
@@ -13,10 +15,42 @@ int b200_fail_cuda(const char *what, cudaError_t e);   // same, with the CUDA er
         if (e__ != cudaSuccess) return b200_fail_cuda(#call, e__); \
     } while (0)
 
+// No C++ exception may cross the C ABI: entries whose bodies allocate (std::vector, std::string) run inside this.
+template <class F>
+static inline int b200_guarded(F &&f) noexcept {
+    try {
+        return f();
+    } catch (const std::bad_alloc &) {
+        return b200_fail("out of host memory");
+    } catch (const std::exception &e) {
+        return b200_fail(std::string("internal error: ") + e.what());
+    } catch (...) {
+        return b200_fail("internal error");
+    }
+}
+
 namespace b200 {
 // gate prologue coefficients (kernels.cu, shared with the device code)
 void b200_gate_coeffs(int op, int half, int *s0, int *s1, int32_t *cst, int *second);
 }  // namespace b200
+
+// Every entry makes the key's device current for its own duration and puts the caller's device back on return
+// (a multi-GPU host such as torch keeps allocating on the device it selected).
+struct DeviceGuard {
+    int prev = -1;
+    cudaError_t err = cudaSuccess;
+    explicit DeviceGuard(int device) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; cudaGetLastError(); }
+        if (prev != device) err = cudaSetDevice(device);
+        else prev = -1;   // nothing to restore
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    DeviceGuard(const DeviceGuard &) = delete;
+    DeviceGuard &operator=(const DeviceGuard &) = delete;
+};
+#define B200_ON_DEVICE(dev)                                                     \
+    DeviceGuard dev_guard__(dev);                                               \
+    if (dev_guard__.err != cudaSuccess) return b200_fail_cuda("cudaSetDevice", dev_guard__.err)
 
 struct DevBuf {
     void *p = nullptr;
@@ -66,8 +100,25 @@ struct b200_key {
     static constexpr int kSlices = 8;
     cudaStream_t stream_h2d = nullptr, stream_d2h = nullptr;
     cudaEvent_t ev_up[kSlices] = {}, ev_done[kSlices] = {};
-    std::mutex mu;                      // one call at a time per key (shared workspace)
+    std::mutex mu;                      // one ENQUEUE at a time per key (shared workspace)
     DevBuf u, in0, in1, in2, out, nz, desc_rot, desc_ks, desc_lin, desc_io, acc;
+    // The workspaces above are shared by all calls on this key, and the mutex orders only the enqueue, not the
+    // execution: a call on another stream than the previous one first waits (on the device) for the event the
+    // previous call recorded after its last kernel.  scratch_begin / scratch_end bracket every use.
+    cudaEvent_t ev_scratch = nullptr;
+    cudaStream_t scratch_stream = nullptr;
+    bool scratch_used = false;
+    int scratch_begin(cudaStream_t s) {
+        if (scratch_used && scratch_stream != s) B200_CK(cudaStreamWaitEvent(s, ev_scratch, 0));
+        return 0;
+    }
+    int scratch_end(cudaStream_t s) {
+        B200_CK(cudaEventRecord(ev_scratch, s));
+        scratch_stream = s;
+        scratch_used = true;
+        return 0;
+    }
+    uint64_t fingerprint = 0;           // of the libtfhe cloud key this device key was uploaded from (cache validation)
     PinnedBuf stage_in, stage_out;
     // ring of CUDA-event triplets (before blind rotation, between, after key switch), one per gate call
     static constexpr int kRing = 64;

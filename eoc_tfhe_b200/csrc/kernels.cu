@@ -13,7 +13,9 @@
 //   k_cmux_test      a single CMux step / external product on caller accumulators (parity tests)
 #include "engine.cuh"
 #include "negacyclic_fft.cuh"
-#include "negacyclic_fft16.cuh"
+#ifdef B200_EXPERIMENTS
+#include "negacyclic_fft16.cuh"   // round-1 experiments: built only with -DB200_EXPERIMENTS
+#endif
 #include "../../include/b200tfhe.h"
 
 #include <atomic>
@@ -52,6 +54,7 @@ static RootSet make_rootset(int level, unsigned b) {
     w.D = cos_tan(c + pi / 4);
     return w;
 }
+#ifdef B200_EXPERIMENTS
 static RootSet16 make_rootset16(int level, unsigned b) {
     RootSet16 w;
     w.A = cos_tan(block_theta(level, b) / 2);
@@ -64,17 +67,21 @@ static RootSet16 make_rootset16(int level, unsigned b) {
     w.H = cos_tan(block_theta(level + 3, 8 * b + 6) / 2);
     return w;
 }
+#endif
 cudaError_t upload_twiddles() {
     static TwiddleTables h;
     h.p1 = make_rootset(0, 0);
     for (unsigned b = 0; b < 8; ++b) h.p2[b] = make_rootset(3, b);
     for (unsigned b = 0; b < 64; ++b) h.p3[b] = make_rootset(6, b);
     cudaError_t e = cudaMemcpyToSymbol(c_tw, &h, sizeof(h));
+#ifdef B200_EXPERIMENTS
     if (e != cudaSuccess) return e;
     static TwiddleTables16 h16;
     for (unsigned b = 0; b < 2; ++b) h16.p1[b] = make_rootset16(1, b);
     for (unsigned b = 0; b < 32; ++b) h16.p2[b] = make_rootset16(5, b);
-    return cudaMemcpyToSymbol(c_tw16, &h16, sizeof(h16));
+    e = cudaMemcpyToSymbol(c_tw16, &h16, sizeof(h16));
+#endif
+    return e;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -398,10 +405,12 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
 }
 
 }  // namespace b200
+#ifdef B200_EXPERIMENTS
 #include "blind_rotate16.cuh"
 #include "blind_rotate3.cuh"
 #include "blind_rotate4.cuh"
 #include "blind_rotate5.cuh"
+#endif
 #include "blind_rotate_lat.cuh"
 namespace b200 {
 
@@ -602,8 +611,10 @@ cudaError_t launch_bk_convert(const DeviceKey &key, const int32_t *d_bk_coefs, c
     const int polys = key.n * (key.k + 1) * key.l * (key.k + 1);
     k_bk_convert<<<polys, 64, 0, s>>>(d_bk_coefs, key.bkfft);
     COUNT_LAUNCH();
+#ifdef B200_EXPERIMENTS
     k_bk_convert16<<<polys, 32, 0, s>>>(d_bk_coefs, key.bkfft16);
     COUNT_LAUNCH();
+#endif
     return cudaGetLastError();
 }
 
@@ -669,6 +680,13 @@ static cudaError_t br_launch(const DeviceKey &key, const BlindRotateArgs &a, cud
 // (B200_BR_KERNEL=w16 or b200_set_blind_rotate_kernel(1)).
 static std::atomic<int> g_br_variant{-1};
 void set_blind_rotate_variant(int v) { g_br_variant.store(v); }
+bool experiments_built() {
+#ifdef B200_EXPERIMENTS
+    return true;
+#else
+    return false;
+#endif
+}
 static int br_variant() {
     int v = g_br_variant.load();
     if (v < 0) {
@@ -678,6 +696,7 @@ static int br_variant() {
     }
     return v;
 }
+#ifdef B200_EXPERIMENTS
 template <int L, int BGBIT, int G>
 static cudaError_t br16_launch(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
     static bool done[16] = {false};
@@ -693,6 +712,7 @@ static cudaError_t br16_launch(const DeviceKey &key, const BlindRotateArgs &a, c
     k_blind_rotate16<L, BGBIT, G><<<grid, 32 * G, br16_smem_bytes(G), s>>>(key, a);
     return cudaSuccess;
 }
+#endif
 cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
     if (a.items <= 0) return cudaSuccess;
     if (a.items > 0x7fffffffLL || key.n + 1 > 640) return cudaErrorInvalidValue;
@@ -709,6 +729,7 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
             if (el != cudaErrorInvalidValue) return el;
         }
     }
+#ifdef B200_EXPERIMENTS
     if (br_variant() == 8 && a.items >= 148 * 4 && key.l == 2 && (key.Bgbit == 10 || key.Bgbit == 8)) {
         // v5: two warps per ciphertext, each a 16-point-per-thread transform engine owning one polynomial
         // (small batches stay on v2: a lone v5 ciphertext takes 5.6 us per step against 4.3 us)
@@ -764,6 +785,7 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         COUNT_LAUNCH();
         return cudaGetLastError();
     }
+#endif
     // More than one ciphertext per SM: multi-ciphertext CTAs on a balanced grid (br_launch_st).  Measured at
     // l = 2 (ms, G=1 x 3 CTAs per SM / G=4 / G=6): 296 items 2.39 / 2.29 / 2.66; 591: 4.69 / 3.44 / 3.73;
     // 600: - / 5.49 / 4.74; 887: - / 6.48 / 4.92.
@@ -816,6 +838,7 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
 cudaError_t launch_cmux_test(const DeviceKey &key, int32_t *d_acc, int bk_index, int barai, int mode,
                              int64_t count, cudaStream_t s) {
     if (count <= 0) return cudaSuccess;
+#ifdef B200_EXPERIMENTS
     if (br_variant() == 1) {
 #define CT16_LAUNCH(L_, B_)                                                                                      \
     do {                                                                                                         \
@@ -833,6 +856,7 @@ cudaError_t launch_cmux_test(const DeviceKey &key, int32_t *d_acc, int bk_index,
         COUNT_LAUNCH();
         return cudaGetLastError();
     }
+#endif
 #define CT_LAUNCH(L_, B_)                                                                 \
     do {                                                                                  \
         cudaError_t e = set_br_attr<L_, B_, 1>();                                         \

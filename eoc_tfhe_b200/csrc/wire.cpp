@@ -110,86 +110,92 @@ std::string fmt_double(double v) {
 }  // namespace
 
 extern "C" int b200_wire_parse_cloudkey(const void *buf, size_t len, b200_params *p, b200_wire_cloudkey_info *info) {
-    if (!buf || !p || !info) return b200_fail("NULL argument");
-    Cursor c{(const unsigned char *)buf, len, 0};
-    std::string title;
-    std::map<std::string, std::string> m;
-    int64_t iv = 0;
-    double dv = 0;
-    std::memset(info, 0, sizeof *info);
-    // GATEBOOTSPARAMS (tfhe_io.cpp:1014-1029; ks_basebit is read back through getProperty_double there)
-    if (!read_section(c, title, m) || title != "GATEBOOTSPARAMS") return b200_fail("cloud key: GATEBOOTSPARAMS section missing");
-    if (!get_int(m, "ks_t", iv)) return b200_fail("cloud key: ks_t missing");
-    p->ks_t = (int32_t)iv;
-    if (!get_double(m, "ks_basebit", dv)) return b200_fail("cloud key: ks_basebit missing");
-    p->ks_basebit = (int32_t)dv;
-    if (!read_section(c, title, m) || title != "LWEPARAMS") return b200_fail("cloud key: LWEPARAMS section missing");
-    if (!get_int(m, "n", iv)) return b200_fail("cloud key: n missing");
-    p->n = (int32_t)iv;
-    get_double(m, "alpha_min", info->lwe_alpha_min);
-    get_double(m, "alpha_max", info->lwe_alpha_max);
-    if (!read_section(c, title, m) || title != "TLWEPARAMS") return b200_fail("cloud key: TLWEPARAMS section missing");
-    if (!get_int(m, "N", iv)) return b200_fail("cloud key: N missing");
-    p->N = (int32_t)iv;
-    if (!get_int(m, "k", iv)) return b200_fail("cloud key: k missing");
-    p->k = (int32_t)iv;
-    get_double(m, "alpha_min", info->tlwe_alpha_min);
-    get_double(m, "alpha_max", info->tlwe_alpha_max);
-    if (!read_section(c, title, m) || title != "TGSWPARAMS") return b200_fail("cloud key: TGSWPARAMS section missing");
-    if (!get_int(m, "l", iv)) return b200_fail("cloud key: l missing");
-    p->l = (int32_t)iv;
-    if (!get_int(m, "Bgbit", iv)) return b200_fail("cloud key: Bgbit missing");
-    p->Bgbit = (int32_t)iv;
-    if (!read_section(c, title, m) || title != "LWEKSPARAMS") return b200_fail("cloud key: LWEKSPARAMS section missing");
-    int64_t ksn = 0, kst = 0, ksb = 0;
-    if (!get_int(m, "n", ksn) || !get_int(m, "t", kst) || !get_int(m, "basebit", ksb)) return b200_fail("cloud key: LWEKSPARAMS incomplete");
-    if (p->n <= 0 || p->N <= 0 || p->k <= 0 || p->l <= 0 || p->ks_t <= 0 || p->ks_basebit <= 0 || p->ks_basebit > 8)
-        return b200_fail("cloud key: non-positive parameter");
-    if (ksn != (int64_t)p->N * p->k || kst != p->ks_t || ksb != p->ks_basebit)
-        return b200_fail("cloud key: key-switch section does not match the parameter set");
-    // binary blocks
-    int32_t uid = 0;
-    double var = 0;
-    if (!c.bytes(&uid, 4) || uid != kUidKs) return b200_fail("cloud key: key-switch block (uid 200) missing");
-    if (!c.bytes(&var, 8)) return b200_fail("cloud key: truncated");
-    p->ks_variance = var;
-    const size_t ks_ints = (size_t)p->N * p->k * p->ks_t * ((size_t)1 << p->ks_basebit) * (p->n + 1);
-    info->ks_offset = c.pos;
-    info->ks_bytes = ks_ints * 4;
-    if (len - c.pos < info->ks_bytes) return b200_fail("cloud key: key-switch block truncated");
-    c.pos += info->ks_bytes;
-    if (!c.bytes(&uid, 4) || uid != kUidBk) return b200_fail("cloud key: bootstrapping-key block (uid 201) missing");
-    if (!c.bytes(&var, 8)) return b200_fail("cloud key: truncated");
-    info->bk_variance = var;
-    const size_t bk_ints = (size_t)p->n * (p->k + 1) * p->l * (p->k + 1) * p->N;
-    info->bk_offset = c.pos;
-    info->bk_bytes = bk_ints * 4;
-    if (len - c.pos < info->bk_bytes) return b200_fail("cloud key: bootstrapping-key block truncated");
-    info->total_bytes = c.pos + info->bk_bytes;
-    return 0;
+    return b200_guarded([&]() -> int {
+        if (!buf || !p || !info) return b200_fail("NULL argument");
+        Cursor c{(const unsigned char *)buf, len, 0};
+        std::string title;
+        std::map<std::string, std::string> m;
+        int64_t iv = 0;
+        double dv = 0;
+        std::memset(info, 0, sizeof *info);
+        // GATEBOOTSPARAMS (tfhe_io.cpp:1014-1029; ks_basebit is read back through getProperty_double there)
+        if (!read_section(c, title, m) || title != "GATEBOOTSPARAMS") return b200_fail("cloud key: GATEBOOTSPARAMS section missing");
+        if (!get_int(m, "ks_t", iv)) return b200_fail("cloud key: ks_t missing");
+        p->ks_t = (int32_t)iv;
+        if (!get_double(m, "ks_basebit", dv)) return b200_fail("cloud key: ks_basebit missing");
+        p->ks_basebit = (int32_t)dv;
+        if (!read_section(c, title, m) || title != "LWEPARAMS") return b200_fail("cloud key: LWEPARAMS section missing");
+        if (!get_int(m, "n", iv)) return b200_fail("cloud key: n missing");
+        p->n = (int32_t)iv;
+        get_double(m, "alpha_min", info->lwe_alpha_min);
+        get_double(m, "alpha_max", info->lwe_alpha_max);
+        if (!read_section(c, title, m) || title != "TLWEPARAMS") return b200_fail("cloud key: TLWEPARAMS section missing");
+        if (!get_int(m, "N", iv)) return b200_fail("cloud key: N missing");
+        p->N = (int32_t)iv;
+        if (!get_int(m, "k", iv)) return b200_fail("cloud key: k missing");
+        p->k = (int32_t)iv;
+        get_double(m, "alpha_min", info->tlwe_alpha_min);
+        get_double(m, "alpha_max", info->tlwe_alpha_max);
+        if (!read_section(c, title, m) || title != "TGSWPARAMS") return b200_fail("cloud key: TGSWPARAMS section missing");
+        if (!get_int(m, "l", iv)) return b200_fail("cloud key: l missing");
+        p->l = (int32_t)iv;
+        if (!get_int(m, "Bgbit", iv)) return b200_fail("cloud key: Bgbit missing");
+        p->Bgbit = (int32_t)iv;
+        if (!read_section(c, title, m) || title != "LWEKSPARAMS") return b200_fail("cloud key: LWEKSPARAMS section missing");
+        int64_t ksn = 0, kst = 0, ksb = 0;
+        if (!get_int(m, "n", ksn) || !get_int(m, "t", kst) || !get_int(m, "basebit", ksb)) return b200_fail("cloud key: LWEKSPARAMS incomplete");
+        if (p->n <= 0 || p->N <= 0 || p->k <= 0 || p->l <= 0 || p->ks_t <= 0 || p->ks_basebit <= 0 || p->ks_basebit > 8)
+            return b200_fail("cloud key: non-positive parameter");
+        if (ksn != (int64_t)p->N * p->k || kst != p->ks_t || ksb != p->ks_basebit)
+            return b200_fail("cloud key: key-switch section does not match the parameter set");
+        // binary blocks
+        int32_t uid = 0;
+        double var = 0;
+        if (!c.bytes(&uid, 4) || uid != kUidKs) return b200_fail("cloud key: key-switch block (uid 200) missing");
+        if (!c.bytes(&var, 8)) return b200_fail("cloud key: truncated");
+        p->ks_variance = var;
+        const size_t ks_ints = (size_t)p->N * p->k * p->ks_t * ((size_t)1 << p->ks_basebit) * (p->n + 1);
+        info->ks_offset = c.pos;
+        info->ks_bytes = ks_ints * 4;
+        if (len - c.pos < info->ks_bytes) return b200_fail("cloud key: key-switch block truncated");
+        c.pos += info->ks_bytes;
+        if (!c.bytes(&uid, 4) || uid != kUidBk) return b200_fail("cloud key: bootstrapping-key block (uid 201) missing");
+        if (!c.bytes(&var, 8)) return b200_fail("cloud key: truncated");
+        info->bk_variance = var;
+        const size_t bk_ints = (size_t)p->n * (p->k + 1) * p->l * (p->k + 1) * p->N;
+        info->bk_offset = c.pos;
+        info->bk_bytes = bk_ints * 4;
+        if (len - c.pos < info->bk_bytes) return b200_fail("cloud key: bootstrapping-key block truncated");
+        info->total_bytes = c.pos + info->bk_bytes;
+        return 0;
+    });
 }
 
 extern "C" int b200_key_from_cloudkey_bytes(const void *buf, size_t len, b200_key **out) {
-    b200_params p;
-    b200_wire_cloudkey_info info;
-    if (b200_wire_parse_cloudkey(buf, len, &p, &info)) return 1;
-    // the payloads are int32 arrays at arbitrary byte offsets after the text sections: realign
-    std::vector<int32_t> ks(info.ks_bytes / 4), bk(info.bk_bytes / 4);
-    std::memcpy(ks.data(), (const unsigned char *)buf + info.ks_offset, info.ks_bytes);
-    std::memcpy(bk.data(), (const unsigned char *)buf + info.bk_offset, info.bk_bytes);
-    return b200_key_create(&p, bk.data(), ks.data(), out);
+    return b200_guarded([&]() -> int {
+        b200_params p;
+        b200_wire_cloudkey_info info;
+        if (b200_wire_parse_cloudkey(buf, len, &p, &info)) return 1;
+        // the payloads are int32 arrays at arbitrary byte offsets after the text sections: realign
+        std::vector<int32_t> ks(info.ks_bytes / 4), bk(info.bk_bytes / 4);
+        std::memcpy(ks.data(), (const unsigned char *)buf + info.ks_offset, info.ks_bytes);
+        std::memcpy(bk.data(), (const unsigned char *)buf + info.bk_offset, info.bk_bytes);
+        return b200_key_create(&p, bk.data(), ks.data(), out);
+    });
 }
 
 extern "C" int b200_key_from_cloudkey_file(const char *path, b200_key **out) {
-    if (!path) return b200_fail("path is NULL");
-    FILE *f = std::fopen(path, "rb");
-    if (!f) return b200_fail(std::string("cannot open ") + path);
-    std::vector<unsigned char> data;
-    unsigned char chunk[1 << 16];
-    size_t got;
-    while ((got = std::fread(chunk, 1, sizeof chunk, f)) > 0) data.insert(data.end(), chunk, chunk + got);
-    std::fclose(f);
-    return b200_key_from_cloudkey_bytes(data.data(), data.size(), out);
+    return b200_guarded([&]() -> int {
+        if (!path) return b200_fail("path is NULL");
+        FILE *f = std::fopen(path, "rb");
+        if (!f) return b200_fail(std::string("cannot open ") + path);
+        std::vector<unsigned char> data;
+        unsigned char chunk[1 << 16];
+        size_t got;
+        while ((got = std::fread(chunk, 1, sizeof chunk, f)) > 0) data.insert(data.end(), chunk, chunk + got);
+        std::fclose(f);
+        return b200_key_from_cloudkey_bytes(data.data(), data.size(), out);
+    });
 }
 
 extern "C" int64_t b200_wire_cloudkey_size(const b200_params *p) {
@@ -209,32 +215,34 @@ extern "C" int64_t b200_wire_cloudkey_size(const b200_params *p) {
 
 extern "C" int b200_wire_write_cloudkey(void *buf, size_t cap, size_t *written, const b200_params *p,
                                         const b200_wire_cloudkey_info *alphas, const int32_t *bk_coefs, const int32_t *ks_rows) {
-    if (!buf || !p || !bk_coefs || !ks_rows) return b200_fail("NULL argument");
-    const double a0 = alphas ? alphas->lwe_alpha_min : 0, a1 = alphas ? alphas->lwe_alpha_max : 0;
-    const double t0 = alphas ? alphas->tlwe_alpha_min : 0, t1 = alphas ? alphas->tlwe_alpha_max : 0;
-    const double bkvar = alphas ? alphas->bk_variance : 0;
-    std::string h;
-    put_section(h, "GATEBOOTSPARAMS", {{"ks_t", fmt_int(p->ks_t)}, {"ks_basebit", fmt_int(p->ks_basebit)}});
-    put_section(h, "LWEPARAMS", {{"n", fmt_int(p->n)}, {"alpha_min", fmt_double(a0)}, {"alpha_max", fmt_double(a1)}});
-    put_section(h, "TLWEPARAMS", {{"N", fmt_int(p->N)}, {"k", fmt_int(p->k)}, {"alpha_min", fmt_double(t0)}, {"alpha_max", fmt_double(t1)}});
-    put_section(h, "TGSWPARAMS", {{"l", fmt_int(p->l)}, {"Bgbit", fmt_int(p->Bgbit)}});
-    put_section(h, "LWEKSPARAMS", {{"n", fmt_int((int64_t)p->N * p->k)}, {"t", fmt_int(p->ks_t)}, {"basebit", fmt_int(p->ks_basebit)}});
-    const size_t ks_bytes = (size_t)p->N * p->k * p->ks_t * ((size_t)1 << p->ks_basebit) * (p->n + 1) * 4;
-    const size_t bk_bytes = (size_t)p->n * (p->k + 1) * p->l * (p->k + 1) * p->N * 4;
-    const size_t total = h.size() + 12 + ks_bytes + 12 + bk_bytes;
-    if (written) *written = total;
-    if (cap < total) return b200_fail("buffer too small for the cloud key");
-    unsigned char *o = (unsigned char *)buf;
-    std::memcpy(o, h.data(), h.size());
-    o += h.size();
-    std::memcpy(o, &kUidKs, 4);
-    std::memcpy(o + 4, &p->ks_variance, 8);
-    std::memcpy(o + 12, ks_rows, ks_bytes);
-    o += 12 + ks_bytes;
-    std::memcpy(o, &kUidBk, 4);
-    std::memcpy(o + 4, &bkvar, 8);
-    std::memcpy(o + 12, bk_coefs, bk_bytes);
-    return 0;
+    return b200_guarded([&]() -> int {
+        if (!buf || !p || !bk_coefs || !ks_rows) return b200_fail("NULL argument");
+        const double a0 = alphas ? alphas->lwe_alpha_min : 0, a1 = alphas ? alphas->lwe_alpha_max : 0;
+        const double t0 = alphas ? alphas->tlwe_alpha_min : 0, t1 = alphas ? alphas->tlwe_alpha_max : 0;
+        const double bkvar = alphas ? alphas->bk_variance : 0;
+        std::string h;
+        put_section(h, "GATEBOOTSPARAMS", {{"ks_t", fmt_int(p->ks_t)}, {"ks_basebit", fmt_int(p->ks_basebit)}});
+        put_section(h, "LWEPARAMS", {{"n", fmt_int(p->n)}, {"alpha_min", fmt_double(a0)}, {"alpha_max", fmt_double(a1)}});
+        put_section(h, "TLWEPARAMS", {{"N", fmt_int(p->N)}, {"k", fmt_int(p->k)}, {"alpha_min", fmt_double(t0)}, {"alpha_max", fmt_double(t1)}});
+        put_section(h, "TGSWPARAMS", {{"l", fmt_int(p->l)}, {"Bgbit", fmt_int(p->Bgbit)}});
+        put_section(h, "LWEKSPARAMS", {{"n", fmt_int((int64_t)p->N * p->k)}, {"t", fmt_int(p->ks_t)}, {"basebit", fmt_int(p->ks_basebit)}});
+        const size_t ks_bytes = (size_t)p->N * p->k * p->ks_t * ((size_t)1 << p->ks_basebit) * (p->n + 1) * 4;
+        const size_t bk_bytes = (size_t)p->n * (p->k + 1) * p->l * (p->k + 1) * p->N * 4;
+        const size_t total = h.size() + 12 + ks_bytes + 12 + bk_bytes;
+        if (written) *written = total;
+        if (cap < total) return b200_fail("buffer too small for the cloud key");
+        unsigned char *o = (unsigned char *)buf;
+        std::memcpy(o, h.data(), h.size());
+        o += h.size();
+        std::memcpy(o, &kUidKs, 4);
+        std::memcpy(o + 4, &p->ks_variance, 8);
+        std::memcpy(o + 12, ks_rows, ks_bytes);
+        o += 12 + ks_bytes;
+        std::memcpy(o, &kUidBk, 4);
+        std::memcpy(o + 4, &bkvar, 8);
+        std::memcpy(o + 12, bk_coefs, bk_bytes);
+        return 0;
+    });
 }
 
 // ---- LWE samples ------------------------------------------------------------------------------------

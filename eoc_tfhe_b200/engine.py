@@ -292,6 +292,11 @@ def set_blind_rotate_kernel(variant):
     _lib.check(_lib.load().b200_set_blind_rotate_kernel(int(v)))
 
 
+def experiments_built():
+    """True when the library carries the round-1 blind-rotation variants (-DB200_EXPERIMENTS)."""
+    return bool(_lib.load().b200_experiments_built())
+
+
 def set_keyswitch_kernel(variant):
     """0 / "auto": by batch size; 1 / "gather": 8-sample tiles; 2 / "stream": table streamed by TMA, 64 samples per CTA."""
     v = {"auto": 0, "gather": 1, "stream": 2}.get(variant, variant)

@@ -65,6 +65,7 @@ SIGNATURES = {
     "b200_wire_read_samples": (C.c_int, [_VP, C.c_size_t, C.c_int32, C.c_int64, _VP, _VP]),
     "b200_wire_write_samples": (C.c_int, [_VP, C.c_size_t, C.c_int32, C.c_int64, _VP, _VP]),
     "b200_set_blind_rotate_kernel": (C.c_int, [C.c_int]),
+    "b200_experiments_built": (C.c_int, []),
     "b200_set_keyswitch_kernel": (C.c_int, [C.c_int]),
     "bootsGate_batch": (C.c_int, [C.c_int, _VP, _VP, _VP, _VP, C.c_int32, _VP]),
     # eoc evaluation-side entry points (csrc/eoc_abi.cpp); strings come back as new[] pointers

@@ -156,6 +156,14 @@ void tfhe_bootstrap_FFT     (struct LweSample *result, const struct LweBootstrap
 void tfhe_bootstrap_woKS_FFT(struct LweSample *result, const struct LweBootstrappingKeyFFT *bk, Torus32 mu, const struct LweSample *x);  /* lwe-bootstrapping-functions-fft.cpp:169 */
 void lweKeySwitch           (struct LweSample *result, const struct LweKeySwitchKey *ks, const struct LweSample *sample);               /* lwe-keyswitch-functions.cpp:228 */
 
+/* libtfhe's key destructors, interposed so that the device key cached for a host key dies with it: they drop the
+ * cache entry (b200_cloudkey_forget) and then call libtfhe's own definition, found with dlsym(RTLD_NEXT) -- so
+ * they do their job only in the drop-in link order (this library before libtfhe).  Independently of them a cache
+ * hit is re-validated against a fingerprint of the key material, so a new key set that malloc placed at a deleted
+ * one's address is uploaded afresh instead of being evaluated with the old device key. */
+void delete_gate_bootstrapping_cloud_keyset(struct TFheGateBootstrappingCloudKeySet *keyset);  /* tfhe_gate_bootstrapping.cpp:124 */
+void delete_LweBootstrappingKeyFFT(struct LweBootstrappingKeyFFT *obj);                        /* lwe-bootstrapping-functions-fft.cpp:290 */
+
 /* ------------------------------------------------------------------------------------------
  * 2. Batched gate over libtfhe samples (new).
  *    Snapshot semantics: every input of the batch is read before any output is written, so
@@ -221,7 +229,15 @@ int  b200_key_device_blobs(const b200_key *key, void **d_bkfft, size_t *bkfft_by
 int  b200_gate_batch_host(b200_key *key, int op, int32_t *out, const int32_t *a, const int32_t *b,
                           const int32_t *c, int64_t count);
 /* Gates on DEVICE-resident batches; `stream` is a cudaStream_t (NULL = default stream).
- * Asynchronous: returns after enqueueing. out must not overlap inputs. */
+ * Asynchronous: returns after enqueueing. out must not overlap inputs.
+ * Streams: a key owns one set of device workspaces (extracted samples, descriptors).  Calls on one key may come
+ * from any stream and any host thread: the enqueue is serialised by a mutex, and a call on a different stream
+ * than the previous call on that key first waits -- on the device, via an event -- for the previous call's last
+ * kernel.  Calls on DIFFERENT keys never wait for each other.  The *_host entries use the key's own stream and
+ * follow the same rule, so mixing *_dev and *_host calls on one key is safe.
+ * Device: every entry makes the key's device current while it runs and restores the caller's device on return.
+ * Timing (b200_last_timing_ms / b200_timing_drain): covers the first blind-rotation + key-switch launch pair of
+ * a call; a call that is split into chunks (> 2^18 rotations) or pipelined slices reports its first chunk. */
 int  b200_gate_batch_dev(b200_key *key, int op, int32_t *d_out, const int32_t *d_a,
                          const int32_t *d_b, const int32_t *d_c, int64_t count, void *stream);
 
@@ -346,6 +362,9 @@ int  b200_fp64_peak_tflops(int device, double *tflops);
  * choice is a performance knob that bench.py and the parity tests exercise.  Batches of at most one
  * ciphertext per SM use the latency kernel (one ciphertext per CTA) while the variant is 0.  Also settable with B200_BR_KERNEL=v2|w16|<number> before first use. */
 int  b200_set_blind_rotate_kernel(int variant);
+/* 1 when the library was compiled with -DB200_EXPERIMENTS, i.e. variants 1..8 above exist; the shipped build has
+ * variant 0 only and b200_set_blind_rotate_kernel(v != 0) fails. */
+int  b200_experiments_built(void);
 /* Key-switch kernel: 0 = chosen by batch size (default), 1 = gather kernel (8-sample tiles, any batch),
  * 2 = table-streaming kernel (64 samples per CTA, table rows staged by TMA).  Results are identical. */
 int  b200_set_keyswitch_kernel(int variant);

@@ -18,8 +18,10 @@ pytestmark = [pytest.mark.gpu,
 @pytest.fixture(scope="module", params=[(80, "v2"), (128, "v2"), (80, "w16"), (128, "w16")],
                 ids=["P80-v2", "P128-v2", "P80-w16", "P128-w16"])
 def keys(request):
-    from eoc_tfhe_b200 import CloudKey, set_blind_rotate_kernel
+    from eoc_tfhe_b200 import CloudKey, set_blind_rotate_kernel, experiments_built
     lam, kernel = request.param
+    if kernel != "v2" and not experiments_built():
+        pytest.skip("round-1 variant: built only with B200_EXPERIMENTS=1")
     set_blind_rotate_kernel(kernel)
     ref = reflib.RefLib()
     rk = ref.keygen(lam, seed=42)

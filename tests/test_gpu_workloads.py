@@ -263,7 +263,9 @@ def test_tensor_memory_blind_rotation_variants_bit_identical(p80):
     integer convolution that the FP64 transforms resolve with a rounding margin far below 1/2, so any correct
     kernel, whatever its summation order, must produce the SAME extracted samples word for word -- including
     a ragged tail and an all-zero input (every bara_i = 0, all steps skipped)."""
-    from eoc_tfhe_b200 import set_blind_rotate_kernel
+    from eoc_tfhe_b200 import set_blind_rotate_kernel, experiments_built
+    if not experiments_built():
+        pytest.skip("round-1 variants are built only with B200_EXPERIMENTS=1 (python __graft_entry__.py)")
     rk, ck = p80
     rng = np.random.default_rng(77)
     x = rng.integers(-2**31, 2**31, size=(148 * 4 + 13, rk.n + 1), dtype=np.int64).astype(np.int32)
