@@ -133,15 +133,15 @@ __global__ void __launch_bounds__(128 * L, 1) k_blind_rotate_lat(const DeviceKey
 #pragma unroll
                 for (int r = 0; r < 8; ++r) { const double2 v = pg[r * 64]; s[r].x += v.x; s[r].y += v.y; }
             }
-            negacyclic_inverse(s, bufs + toggle * kBufElems, t, w2, w3, bar);
+            negacyclic_inverse<true>(s, bufs + toggle * kBufElems, t, w2, w3, bar);
             toggle ^= 1;
-            constexpr double kScale = 1.0 / kM;
             int32_t *Q = ACC + g * kN;
 #pragma unroll
             for (int r = 0; r < 8; ++r) {
                 const int j = t + 64 * r;
-                Q[j] += round_scaled_to_torus(s[r].x, kScale);
-                Q[j + kM] += round_scaled_to_torus(s[r].y, kScale);
+                const double sc = c_tw.p1_scale[r];   // 1/512 times the cos factors the last pass left out
+                Q[j] += round_scaled_to_torus(s[r].x, sc);
+                Q[j + kM] += round_scaled_to_torus(s[r].y, sc);
             }
         }
         __syncthreads();   // accumulator complete; partial buffers free

@@ -73,6 +73,15 @@ cudaError_t upload_twiddles() {
     h.p1 = make_rootset(0, 0);
     for (unsigned b = 0; b < 8; ++b) h.p2[b] = make_rootset(3, b);
     for (unsigned b = 0; b < 64; ++b) h.p3[b] = make_rootset(6, b);
+    {
+        // deferred cos factors of the last inverse pass (negacyclic_fft.cuh, inv_radix8_last), in long double
+        const long double pi = 3.14159265358979323846264338327950288L;
+        const long double cA = cosl(block_theta(0, 0) / 2), cB = cosl(block_theta(1, 0) / 2);
+        const long double cC = cosl(block_theta(2, 0) / 2), cD = cosl(block_theta(2, 0) / 2 + pi / 4);
+        h.p1_rho = (double)(cD / cC);
+        const long double sc[8] = {1, cC, cB, cC * cB, cA, cC * cA, cB * cA, cC * cB * cA};
+        for (int r = 0; r < 8; ++r) h.p1_scale[r] = (double)(sc[r] / 512);
+    }
     cudaError_t e = cudaMemcpyToSymbol(c_tw, &h, sizeof(h));
 #ifdef B200_EXPERIMENTS
     if (e != cudaSuccess) return e;
@@ -282,21 +291,22 @@ __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int
             rows.release(q * L + p);
         }
     }
-    constexpr double kScale = 1.0 / kM;
-    negacyclic_inverse(acc0, bufs + toggle * kBufElems, t, w2, w3, bar);
+    negacyclic_inverse<true>(acc0, bufs + toggle * kBufElems, t, w2, w3, bar);
     toggle ^= 1;
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         const int j = t + 64 * r;
-        const int32_t lo = round_scaled_to_torus(acc0[r].x, kScale), hi = round_scaled_to_torus(acc0[r].y, kScale);
+        const double sc = c_tw.p1_scale[r];   // 1/512 times the cos factors the last pass left out
+        const int32_t lo = round_scaled_to_torus(acc0[r].x, sc), hi = round_scaled_to_torus(acc0[r].y, sc);
         if (MODE == 0) { ACC[j] += lo; ACC[j + kM] += hi; }
         else           { ACC[j] = lo;  ACC[j + kM] = hi; }
     }
-    negacyclic_inverse(acc1, bufs + toggle * kBufElems, t, w2, w3, bar);
+    negacyclic_inverse<true>(acc1, bufs + toggle * kBufElems, t, w2, w3, bar);
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         const int j = kN + t + 64 * r;
-        const int32_t lo = round_scaled_to_torus(acc1[r].x, kScale), hi = round_scaled_to_torus(acc1[r].y, kScale);
+        const double sc = c_tw.p1_scale[r];
+        const int32_t lo = round_scaled_to_torus(acc1[r].x, sc), hi = round_scaled_to_torus(acc1[r].y, sc);
         if (MODE == 0) { ACC[j] += lo; ACC[j + kM] += hi; }
         else           { ACC[j] = lo;  ACC[j + kM] = hi; }
     }

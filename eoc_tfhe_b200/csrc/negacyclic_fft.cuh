@@ -41,6 +41,10 @@ struct TwiddleTables {
     RootSet p1;                   // level 0, block 0            (warp uniform)
     RootSet p2[8];                // level 3, block = e >> 6
     RootSet p3[64];               // level 6, block = e >> 3
+    // last inverse pass with its cos factors deferred (inv_radix8_last): ratio cos D / cos C and, per register,
+    // the product of the cos factors it skipped times 1/512 -- folded into the rounding FMA
+    double p1_rho;
+    double p1_scale[8];
 };
 
 __constant__ TwiddleTables c_tw;
@@ -128,6 +132,48 @@ __device__ __forceinline__ void inv_radix8(double2 (&x)[8], const RootSet &w) {
     gs_bfly(x[3], x[7], w.A);
 }
 
+// Last inverse pass (warp-uniform roots from the constant bank): the butterflies leave out the multiplication by
+// cos (6 FP64 operations instead of 8); what each register is short of is a constant, c_tw.p1_scale[r], which the
+// caller folds into the rounding FMA.  Where a level adds two registers that are short of different factors
+// (cos C against cos D) the second enters with their ratio: u +- rho v is two DFMA instead of two DADD.
+// (tools/fft_model.py checks the algebra: inv_radix8 == inv_radix8_last followed by the per-register scale.)
+__device__ __forceinline__ void gsu_bfly(double2 &u, double2 &v, const double t) {
+    const double dr = u.x - v.x, di = u.y - v.y;
+    u.x += v.x;
+    u.y += v.y;
+    v.x = fma(t, di, dr);
+    v.y = fma(-t, dr, di);
+}
+__device__ __forceinline__ void gsu_bfly_i(double2 &u, double2 &v, const double t) {
+    const double ndr = v.x - u.x, di = u.y - v.y;   // (wr, wi) * (-i) = (wi, -wr), written without a negation
+    u.x += v.x;
+    u.y += v.y;
+    v.x = fma(t, ndr, di);
+    v.y = fma(-t, di, ndr);
+}
+__device__ __forceinline__ void gsu_bfly_rho(double2 &u, double2 &v, const double t, const double rho) {
+    const double dr = fma(-rho, v.x, u.x), di = fma(-rho, v.y, u.y);
+    u.x = fma(rho, v.x, u.x);
+    u.y = fma(rho, v.y, u.y);
+    v.x = fma(t, di, dr);
+    v.y = fma(-t, dr, di);
+}
+__device__ __forceinline__ void inv_radix8_last(double2 (&x)[8]) {
+    const double tA = c_tw.p1.A.y, tB = c_tw.p1.B.y, tC = c_tw.p1.C.y, tD = c_tw.p1.D.y, rho = c_tw.p1_rho;
+    gsu_bfly(x[0], x[1], tC);
+    gsu_bfly_i(x[2], x[3], tC);
+    gsu_bfly(x[4], x[5], tD);
+    gsu_bfly_i(x[6], x[7], tD);
+    gsu_bfly(x[0], x[2], tB);
+    gsu_bfly(x[1], x[3], tB);
+    gsu_bfly_i(x[4], x[6], tB);
+    gsu_bfly_i(x[5], x[7], tB);
+    gsu_bfly(x[0], x[4], tA);
+    gsu_bfly_rho(x[1], x[5], tA, rho);
+    gsu_bfly(x[2], x[6], tA);
+    gsu_bfly_rho(x[3], x[7], tA, rho);
+}
+
 // Group-wide barrier hook: the kernels pass a functor so that a CTA may hold one or several
 // 64-thread groups (named barriers) without changing the transform code.
 struct CtaBarrier {
@@ -165,7 +211,9 @@ __device__ __forceinline__ void negacyclic_forward(double2 (&x)[8], double2 *buf
 }
 
 // evaluations (pass-3 layout) -> 512 * coefficients (pass-1 layout)
-template <class Barrier>
+// DEFER_LAST: the result in register r is short of the factor 512 * c_tw.p1_scale[r] (see inv_radix8_last): the
+// caller rounds with round_scaled_to_torus(x[r], c_tw.p1_scale[r]) instead of (x[r], 1/512).
+template <bool DEFER_LAST = false, class Barrier>
 __device__ __forceinline__ void negacyclic_inverse(double2 (&x)[8], double2 *buf, const int t,
                                                    const RootSet &w2, const RootSet &w3,
                                                    const Barrier &bar) {
@@ -182,7 +230,8 @@ __device__ __forceinline__ void negacyclic_inverse(double2 (&x)[8], double2 *buf
     bar();
 #pragma unroll
     for (int r = 0; r < 8; ++r) x[r] = buf[pad_idx(t + 64 * r)];
-    inv_radix8(x, c_tw.p1);
+    if (DEFER_LAST) inv_radix8_last(x);
+    else inv_radix8(x, c_tw.p1);
 }
 
 // exact int32 -> double for |v| < 2^31 with one integer op and one DADD (no I2F on the slow pipe)

@@ -127,3 +127,73 @@ if __name__ == "__main__":
         need = check_pass(lay, lv)
         print(name, "thread local; roots per thread:", len(need[0]), "distinct root sets:", len({frozenset(v) for v in need.values()}))
     assert p1.elem(5, 3) == 5 + 64 * 3 and p2.elem(13, 2) == 64 * 1 + 5 + 8 * 2 and p3.elem(7, 4) == 8 * 7 + 4
+
+
+# ---------------------------------------------------------------------------------------------------
+# inverse radix-8 pass with the cos factors deferred (negacyclic_fft.cuh inv_radix8_deferred): algebra check
+# ---------------------------------------------------------------------------------------------------
+def ct(level, b):
+    a = theta(level, b) / 2
+    return math.cos(a), math.tan(a)
+
+
+def gs(u, v, c, t):          # (a, b) <- (a + b, (a - b) conj(s)),  s = c (1 + i t)
+    d = u - v
+    return u + v, c * complex(d.real + t * d.imag, d.imag - t * d.real)
+
+
+def gs_i(u, v, c, t):        # root i s: conj(i s) = -i conj(s)
+    d = u - v
+    w = complex(d.real + t * d.imag, d.imag - t * d.real)
+    return u + v, c * complex(w.imag, -w.real)
+
+
+def inv_radix8(x, A, B, C, D):
+    x = list(x)
+    x[0], x[1] = gs(x[0], x[1], *C); x[2], x[3] = gs_i(x[2], x[3], *C)
+    x[4], x[5] = gs(x[4], x[5], *D); x[6], x[7] = gs_i(x[6], x[7], *D)
+    x[0], x[2] = gs(x[0], x[2], *B); x[1], x[3] = gs(x[1], x[3], *B)
+    x[4], x[6] = gs_i(x[4], x[6], *B); x[5], x[7] = gs_i(x[5], x[7], *B)
+    for r in range(4):
+        x[r], x[r + 4] = gs(x[r], x[r + 4], *A)
+    return x
+
+
+def gsu(u, v, t, rho=None, rot=False):     # unscaled: (a + rho b, (a - rho b)(1 - i t)) [then * -i if rot]
+    if rho is None:
+        s, d = u + v, u - v
+    else:
+        s, d = u + rho * v, u - rho * v     # two FMA per component instead of two ADD
+    w = complex(d.real + t * d.imag, d.imag - t * d.real)
+    return s, (complex(w.imag, -w.real) if rot else w)
+
+
+def inv_radix8_deferred(x, A, B, C, D):
+    """same result as inv_radix8 after multiplying x[r] by scale[r]: 6 FP64 ops per butterfly + 14 scalings"""
+    x = list(x)
+    cA, tA = A; cB, tB = B; cC, tC = C; cD, tD = D
+    x[0], x[1] = gsu(x[0], x[1], tC); x[2], x[3] = gsu(x[2], x[3], tC, rot=True)
+    x[4], x[5] = gsu(x[4], x[5], tD); x[6], x[7] = gsu(x[6], x[7], tD, rot=True)
+    # pending: [1, cC, 1, cC, 1, cD, 1, cD]
+    x[0], x[2] = gsu(x[0], x[2], tB); x[1], x[3] = gsu(x[1], x[3], tB)
+    x[4], x[6] = gsu(x[4], x[6], tB, rot=True); x[5], x[7] = gsu(x[5], x[7], tB, rot=True)
+    # pending: [1, cC, cB, cC cB, 1, cD, cB, cD cB]
+    rho = cD / cC
+    x[0], x[4] = gsu(x[0], x[4], tA)
+    x[1], x[5] = gsu(x[1], x[5], tA, rho=rho)
+    x[2], x[6] = gsu(x[2], x[6], tA)
+    x[3], x[7] = gsu(x[3], x[7], tA, rho=rho)
+    scale = [1, cC, cB, cC * cB, cA, cC * cA, cB * cA, cC * cB * cA]
+    return x, scale
+
+
+if __name__ == "__main__":
+    rng = np.random.default_rng(2)
+    worst = 0.0
+    for level, b in ((0, 0), (3, 5), (6, 37)):
+        A = ct(level, b); B = ct(level + 1, 2 * b); C = ct(level + 2, 4 * b); D = ct(level + 2, 4 * b + 2)
+        x = rng.normal(size=8) + 1j * rng.normal(size=8)
+        want = inv_radix8(x, A, B, C, D)
+        got, scale = inv_radix8_deferred(x, A, B, C, D)
+        worst = max(worst, max(abs(w - g * s) for w, g, s in zip(want, got, scale)))
+    print("deferred-cos inverse radix-8 vs plain: max err %.2e" % worst)
