@@ -66,8 +66,8 @@ extern "C" int b200_set_device(int device) {
 }
 extern "C" int64_t b200_launch_count(void) { return launch_count(); }
 extern "C" int b200_set_blind_rotate_kernel(int variant) {
-    if (variant < 0 || variant > 8) return b200_fail("blind-rotation kernel variant must be 0..8");
-    if (variant != 0 && !experiments_built())
+    if (variant < 0 || variant > 10) return b200_fail("blind-rotation kernel variant must be 0..10");
+    if (variant != 0 && variant < 9 && !experiments_built())
         return b200_fail("blind-rotation variants 1..8 are round-1 experiments: rebuild with -DB200_EXPERIMENTS");
     set_blind_rotate_variant(variant);
     return 0;
@@ -109,10 +109,10 @@ static int key_alloc(const b200_params *p, b200_key **out) {
     // the evaluation-domain key is one blob (one broadcast replicates it); an experiments build appends the
     // layout of the warp-per-ciphertext transform
     const size_t bk_elems = (size_t)d.n * kpl * (d.k + 1) * (d.N / 2);
-    d.bkfft_bytes = (experiments_built() ? 2 : 1) * bk_elems * sizeof(double2);
+    d.bkfft_bytes = (experiments_built() ? 3 : 2) * bk_elems * sizeof(double2);
     d.ks_bytes = (size_t)d.N * d.k * d.ks_t * (base - 1) * d.ks_stride * sizeof(int32_t);
     cudaError_t e = cudaMalloc((void **)&d.bkfft, d.bkfft_bytes);
-    if (e == cudaSuccess) d.bkfft16 = d.bkfft + bk_elems;
+    if (e == cudaSuccess) { d.bkfft_tm = d.bkfft + bk_elems; d.bkfft16 = d.bkfft + 2 * bk_elems; }
     if (e == cudaSuccess) e = cudaMalloc((void **)&d.ks, d.ks_bytes);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&k->stream_h2d, cudaStreamNonBlocking);

@@ -24,7 +24,8 @@ struct DeviceKey {
     int ks_stride;            // n+1 rounded up to a multiple of 4 (int4 loads)
     double ks_variance;
     double2 *bkfft;           // [n][kpl][k+1][8][64]  evaluation domain, pass-3 layout of the 64-thread transform
-    double2 *bkfft16;         // [n][kpl][k+1][16][32] evaluation domain, [r][lane] layout of the warp transform
+    double2 *bkfft_tm;        // same shape, evaluation order of the tensor-memory transform (negacyclic_fft_tm.cuh)
+    double2 *bkfft16;         // [n][kpl][k+1][16][32] evaluation domain, [r][lane] layout of the warp transform (experiments)
     int32_t *ks;              // [N*k][t][base-1][ks_stride]
     size_t bkfft_bytes, ks_bytes;
     int device;

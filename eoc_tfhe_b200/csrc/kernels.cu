@@ -13,11 +13,13 @@
 //   k_cmux_test      a single CMux step / external product on caller accumulators (parity tests)
 #include "engine.cuh"
 #include "negacyclic_fft.cuh"
+#include "negacyclic_fft_tm.cuh"
 #ifdef B200_EXPERIMENTS
 #include "negacyclic_fft16.cuh"   // round-1 experiments: built only with -DB200_EXPERIMENTS
 #endif
 #include "../../include/b200tfhe.h"
 
+#include <algorithm>
 #include <atomic>
 #include <math.h>
 #include <stdlib.h>
@@ -83,6 +85,26 @@ cudaError_t upload_twiddles() {
         for (int r = 0; r < 8; ++r) h.p1_scale[r] = (double)(sc[r] / 512);
     }
     cudaError_t e = cudaMemcpyToSymbol(c_tw, &h, sizeof(h));
+    if (e != cudaSuccess) return e;
+    {
+        // per-thread roots of the small passes of the tensor-memory transform (negacyclic_fft_tm.cuh): P3a is
+        // indexed by b' = e >> 4, P3b by the thread (P3b layout: warp e8, lane (e6 e5 e4 e2 e3), registers (e0 e7 e1))
+        static TmRootTables ht;
+        for (unsigned b = 0; b < 32; ++b) {
+            ht.p3a[b][0] = cos_tan(block_theta(6, 2 * b) / 2);
+            ht.p3a[b][1] = cos_tan(block_theta(7, 4 * b) / 2);
+            ht.p3a[b][2] = cos_tan(block_theta(7, 4 * b + 2) / 2);
+        }
+        for (unsigned t = 0; t < 64; ++t) {
+            const unsigned lane = t & 31, e8 = t >> 5, e6 = (lane >> 4) & 1, e5 = (lane >> 3) & 1, e4 = (lane >> 2) & 1,
+                           e2 = (lane >> 1) & 1, e3 = lane & 1;
+            for (unsigned e7 = 0; e7 < 2; ++e7) {
+                const unsigned e = (e8 << 8) | (e7 << 7) | (e6 << 6) | (e5 << 5) | (e4 << 4) | (e3 << 3) | (e2 << 2);  // e1 = e0 = 0
+                ht.p3b[t][e7] = cos_tan(block_theta(8, e >> 1) / 2);
+            }
+        }
+        e = cudaMemcpyToSymbol(c_tw_tm, &ht, sizeof(ht));
+    }
 #ifdef B200_EXPERIMENTS
     if (e != cudaSuccess) return e;
     static TwiddleTables16 h16;
@@ -96,19 +118,52 @@ cudaError_t upload_twiddles() {
 // ------------------------------------------------------------------------------------------------
 // one-time key conversion
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(64) k_bk_convert(const int32_t *__restrict__ coefs, double2 *__restrict__ out) {
-    __shared__ double2 buf[kBufElems];
+// tensor memory of a CTA: all 512 columns, allocated by warp 0; every warp gets a 128-column window in its own lane
+// quarter (a warp reaches lanes 32 (warp % 4) .. +31 only); warps that share a quarter get different columns
+__device__ __forceinline__ uint32_t tm_alloc_cta(uint32_t *slot, const int window = kTmColsPerWarp) {
+    if (threadIdx.x < 32) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((uint32_t)__cvta_generic_to_shared(slot)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t warp = threadIdx.x >> 5;
+    return *slot + (((warp & 3u) * 32u) << 16) + (warp >> 2) * (uint32_t)window;
+}
+__device__ __forceinline__ void tm_free_cta(const uint32_t *slot) {
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(*slot) : "memory");
+}
+template <class FFT> struct UsesTm { static constexpr bool value = false; };
+template <> struct UsesTm<FftTm> { static constexpr bool value = true; };
+template <> struct UsesTm<FftTmAcc> { static constexpr bool value = true; };
+template <class FFT> struct TmWindow { static constexpr int value = kTmColsPerWarp; };
+template <> struct TmWindow<FftTmAcc> { static constexpr int value = kTmColsPerWarpAcc; };
+
+template <class FFT>
+__global__ void __launch_bounds__(64) k_bk_convert(const int32_t *__restrict__ coefs, double2 *__restrict__ out, int polys) {
+    __shared__ double2 buf[FFT::kBufElemsPerTransform];
+    __shared__ uint32_t tm_slot_s;
     const int t = threadIdx.x;
-    const int32_t *p = coefs + (size_t)blockIdx.x * kN;
-    double2 x[8];
+    uint32_t tm = 0;
+    if (UsesTm<FFT>::value) tm = tm_alloc_cta(&tm_slot_s);
+    FFT fft;
+    fft.init(t, tm);
+    for (int poly = blockIdx.x; poly < polys; poly += gridDim.x) {
+        const int32_t *p = coefs + (size_t)poly * kN;
+        double2 x[8];
 #pragma unroll
-    for (int r = 0; r < 8; ++r)
-        x[r] = make_double2((double)p[t + 64 * r], (double)p[t + 64 * r + kM]);
-    const RootSet w2 = load_rootset(c_tw.p2[t >> 3]), w3 = load_rootset(c_tw.p3[t]);
-    negacyclic_forward(x, buf, t, w2, w3, CtaBarrier());
-    double2 *o = out + (size_t)blockIdx.x * kM;
+        for (int r = 0; r < 8; ++r)
+            x[r] = make_double2((double)p[t + 64 * r], (double)p[t + 64 * r + kM]);
+        fft.forward(x, buf, CtaBarrier());
+        double2 *o = out + (size_t)poly * kM;
 #pragma unroll
-    for (int r = 0; r < 8; ++r) o[r * 64 + t] = x[r];
+        for (int r = 0; r < 8; ++r) o[r * 64 + t] = x[r];
+        __syncthreads();   // the exchange buffer is reused by the next polynomial
+    }
+    if (UsesTm<FFT>::value) tm_free_cta(&tm_slot_s);
 }
 
 __global__ void k_ks_pack(const int32_t *__restrict__ rows, int32_t *__restrict__ out, int n1, int stride,
@@ -235,9 +290,11 @@ struct RingRows {
 //   MODE 0: ACC <- ACC + BK_i (x) ((X^a - 1) ACC)      (lwe-bootstrapping-functions-fft.cpp:67-76)
 //   MODE 1: ACC <- BK_i (x) ACC                         (tgsw-fft-operations.cpp:89-114)
 // ------------------------------------------------------------------------------------------------
-template <int L, int BGBIT, int MODE, class Barrier, class Rows>
+template <int L, int BGBIT, int MODE, class FFT, class Barrier, class Rows>
 __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int a, const Rows &rows,
-                                          const int t, const RootSet &w2, const RootSet &w3, const Barrier &bar) {
+                                          const FFT &fft, const Barrier &bar) {
+    constexpr int kBuf = FFT::kBufElemsPerTransform;
+    const int t = fft.t;
     constexpr uint32_t BG = 1u << BGBIT, HALF = BG >> 1;
     uint32_t offset = 0;  // tgsw.cpp:7-29
 #pragma unroll
@@ -272,7 +329,7 @@ __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int
             for (int r = 0; r < 8; ++r) {
                 x[r] = make_double2(digit_to_double<BGBIT>(dv[r], shift), digit_to_double<BGBIT>(dv[r + 8], shift));
             }
-            negacyclic_forward(x, bufs + toggle * kBufElems, t, w2, w3, bar);
+            fft.forward(x, bufs + toggle * kBuf, bar);
             toggle ^= 1;
             const double2 *row = rows.acquire(q * L + p) + t;
 #pragma unroll
@@ -291,7 +348,7 @@ __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int
             rows.release(q * L + p);
         }
     }
-    negacyclic_inverse<true>(acc0, bufs + toggle * kBufElems, t, w2, w3, bar);
+    fft.template inverse<true>(acc0, bufs + toggle * kBuf, bar);
     toggle ^= 1;
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
@@ -301,7 +358,7 @@ __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int
         if (MODE == 0) { ACC[j] += lo; ACC[j + kM] += hi; }
         else           { ACC[j] = lo;  ACC[j + kM] = hi; }
     }
-    negacyclic_inverse<true>(acc1, bufs + toggle * kBufElems, t, w2, w3, bar);
+    fft.template inverse<true>(acc1, bufs + toggle * kBuf, bar);
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         const int j = kN + t + 64 * r;
@@ -313,28 +370,253 @@ __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int
     bar();  // accumulator complete before the next step's rotated reads
 }
 
+// The same step with the transforms taken two at a time (FftTm::forward2 / inverse2): the digits p, p+1 of one
+// accumulator polynomial go through the forward transform together, the two output columns through the inverse.
+template <int L, int BGBIT, int MODE, class Barrier, class Rows>
+__device__ __forceinline__ void cmux_step_pairs(int32_t *ACC, double2 *bufs, const int a, const Rows &rows,
+                                                const FftTm &fft, const Barrier &bar) {
+    constexpr uint32_t BG = 1u << BGBIT, HALF = BG >> 1;
+    constexpr int kBuf = FftTm::kBufElemsPerTransform;
+    const int t = fft.t;
+    uint32_t offset = 0;  // tgsw.cpp:7-29
+#pragma unroll
+    for (int p = 0; p < L; ++p) offset += HALF << (32 - (p + 1) * BGBIT);
+
+    double2 acc0[8], acc1[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) acc0[r] = acc1[r] = make_double2(0.0, 0.0);
+
+    auto mac = [&](const double2 (&x)[8], int rp) {
+        const double2 *row = rows.acquire(rp) + t;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const double2 b0 = rows.load(row + r * 64);
+            const double2 b1 = rows.load(row + kM + r * 64);
+            acc0[r].x = fma(x[r].x, b0.x, acc0[r].x);
+            acc0[r].x = fma(-x[r].y, b0.y, acc0[r].x);
+            acc0[r].y = fma(x[r].x, b0.y, acc0[r].y);
+            acc0[r].y = fma(x[r].y, b0.x, acc0[r].y);
+            acc1[r].x = fma(x[r].x, b1.x, acc1[r].x);
+            acc1[r].x = fma(-x[r].y, b1.y, acc1[r].x);
+            acc1[r].y = fma(x[r].x, b1.y, acc1[r].y);
+            acc1[r].y = fma(x[r].y, b1.x, acc1[r].y);
+        }
+        rows.release(rp);
+    };
+
+    bool first = true;   // the barrier that ended the previous step also freed the exchange buffers
+#pragma unroll 1
+    for (int q = 0; q < 2; ++q) {
+        const int32_t *P = ACC + q * kN;
+        uint32_t dv[16];  // (rotated difference) + decomposition offset, coefficient t + 64 rr
+#pragma unroll
+        for (int rr = 0; rr < 16; ++rr) {
+            const int j = t + 64 * rr;
+            if (MODE == 0) {
+                const int m = (j - a) & (2 * kN - 1);
+                int32_t v = P[m & (kN - 1)];
+                if (m & kN) v = -v;
+                dv[rr] = (uint32_t)(v - P[j]) + offset;
+            } else {
+                dv[rr] = (uint32_t)P[j] + offset;
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < L; p += 2) {
+            if (!first) bar();   // every thread of the group has read the previous transforms' exchange buffers
+            first = false;
+            const int shift = 32 - (p + 1) * BGBIT;
+            double2 xa[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+                xa[r] = make_double2(digit_to_double<BGBIT>(dv[r], shift), digit_to_double<BGBIT>(dv[r + 8], shift));
+            if (p + 1 < L) {
+                double2 xb[8];
+#pragma unroll
+                for (int r = 0; r < 8; ++r)
+                    xb[r] = make_double2(digit_to_double<BGBIT>(dv[r], shift - BGBIT), digit_to_double<BGBIT>(dv[r + 8], shift - BGBIT));
+                fft.forward2(xa, xb, bufs, bufs + kBuf, bar);
+                mac(xa, q * L + p);
+                mac(xb, q * L + p + 1);
+            } else {
+                fft.forward(xa, bufs, bar);
+                mac(xa, q * L + p);
+            }
+        }
+    }
+    bar();
+    fft.template inverse2<true>(acc0, acc1, bufs, bufs + kBuf, bar);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const int j = t + 64 * r;
+        const double sc = c_tw.p1_scale[r];   // 1/512 times the cos factors the last pass left out
+        const int32_t lo0 = round_scaled_to_torus(acc0[r].x, sc), hi0 = round_scaled_to_torus(acc0[r].y, sc);
+        const int32_t lo1 = round_scaled_to_torus(acc1[r].x, sc), hi1 = round_scaled_to_torus(acc1[r].y, sc);
+        if (MODE == 0) { ACC[j] += lo0; ACC[j + kM] += hi0; ACC[kN + j] += lo1; ACC[kN + j + kM] += hi1; }
+        else           { ACC[j] = lo0;  ACC[j + kM] = hi0;  ACC[kN + j] = lo1;  ACC[kN + j + kM] = hi1; }
+    }
+    bar();  // accumulator complete before the next step's rotated reads; exchange buffers free
+}
+template <int L, int BGBIT, int MODE, class Barrier, class Rows>
+__device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int a, const Rows &rows,
+                                          const FftTm &fft, const Barrier &bar) {
+    cmux_step_pairs<L, BGBIT, MODE>(ACC, bufs, a, rows, fft, bar);
+}
+
+// The pair-wise step with the spectral accumulators in TENSOR MEMORY while the next pair's forward transforms run:
+// the 64 accumulator registers exist only inside a MAC (half of them at a time) and inside the inverse transforms,
+// so six groups per SM have about 40 registers per thread more for the transforms than with resident accumulators.
+// One tcgen05.st + one tcgen05.ld of 256 bytes per thread per step at l = 2 (three of each at l = 3).
+template <int L, int BGBIT, int MODE, class Barrier, class Rows>
+__device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *bufs, const int a, const Rows &rows,
+                                                      const FftTmAcc &fft, const Barrier &bar) {
+    constexpr uint32_t BG = 1u << BGBIT, HALF = BG >> 1;
+    constexpr int kBuf = FftTm::kBufElemsPerTransform;
+    constexpr int kEvents = 2 * ((L + 1) / 2);      // MAC events of one step (a pair of rows, or a single last row)
+    const int t = fft.t;
+    const uint32_t tm_acc = fft.tm + kTmColAcc;
+    uint32_t offset = 0;  // tgsw.cpp:7-29
+#pragma unroll
+    for (int p = 0; p < L; ++p) offset += HALF << (32 - (p + 1) * BGBIT);
+
+    double2 acc0[8], acc1[8];   // defined by the last MAC event only
+
+    // one half (registers 4h .. 4h+3) of a MAC event over NX rows: c += x . key
+    auto mac_half = [&](double2 (&c0)[4], double2 (&c1)[4], const double2 (&x)[8], const double2 *row, int h) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = 4 * h + i;
+            const double2 b0 = rows.load(row + r * 64);
+            const double2 b1 = rows.load(row + kM + r * 64);
+            c0[i].x = fma(x[r].x, b0.x, c0[i].x);
+            c0[i].x = fma(-x[r].y, b0.y, c0[i].x);
+            c0[i].y = fma(x[r].x, b0.y, c0[i].y);
+            c0[i].y = fma(x[r].y, b0.x, c0[i].y);
+            c1[i].x = fma(x[r].x, b1.x, c1[i].x);
+            c1[i].x = fma(-x[r].y, b1.y, c1[i].x);
+            c1[i].y = fma(x[r].x, b1.y, c1[i].y);
+            c1[i].y = fma(x[r].y, b1.x, c1[i].y);
+        }
+    };
+    // event ev over rows rp (and rp + 1 when xb is given)
+    auto mac_event = [&](const int ev, const double2 (&xa)[8], const double2 (*xb)[8], const int rp) {
+        const double2 *rowa = rows.acquire(rp) + t;
+        const double2 *rowb = xb ? rows.acquire(rp + 1) + t : nullptr;
+        if (ev > 0) tm_wait_st();
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            double2 c0[4], c1[4];
+            if (ev == 0) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) c0[i] = c1[i] = make_double2(0.0, 0.0);
+            } else {
+                double d[16], unused[8];
+                tm_load16<0>(d, unused, tm_acc + 32 * h, 0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { c0[i] = make_double2(d[4 * i], d[4 * i + 1]); c1[i] = make_double2(d[4 * i + 2], d[4 * i + 3]); }
+            }
+            mac_half(c0, c1, xa, rowa, h);
+            if (xb) mac_half(c0, c1, *xb, rowb, h);
+            if (ev == kEvents - 1) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { acc0[4 * h + i] = c0[i]; acc1[4 * h + i] = c1[i]; }
+            } else {
+                tm_store16(tm_acc + 32 * h, c0[0].x, c0[0].y, c1[0].x, c1[0].y, c0[1].x, c0[1].y, c1[1].x, c1[1].y,
+                           c0[2].x, c0[2].y, c1[2].x, c1[2].y, c0[3].x, c0[3].y, c1[3].x, c1[3].y);
+            }
+        }
+        rows.release(rp);
+        if (xb) rows.release(rp + 1);
+    };
+
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        const int32_t *P = ACC + q * kN;
+        uint32_t dv[16];  // (rotated difference) + decomposition offset, coefficient t + 64 rr
+#pragma unroll
+        for (int rr = 0; rr < 16; ++rr) {
+            const int j = t + 64 * rr;
+            if (MODE == 0) {
+                const int m = (j - a) & (2 * kN - 1);
+                int32_t v = P[m & (kN - 1)];
+                if (m & kN) v = -v;
+                dv[rr] = (uint32_t)(v - P[j]) + offset;
+            } else {
+                dv[rr] = (uint32_t)P[j] + offset;
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < L; p += 2) {
+            const int ev = q * ((L + 1) / 2) + p / 2;
+            if (ev > 0) bar();   // every thread of the group has read the previous transforms' exchange buffers
+            const int shift = 32 - (p + 1) * BGBIT;
+            double2 xa[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+                xa[r] = make_double2(digit_to_double<BGBIT>(dv[r], shift), digit_to_double<BGBIT>(dv[r + 8], shift));
+            if (p + 1 < L) {
+                double2 xb[8];
+#pragma unroll
+                for (int r = 0; r < 8; ++r)
+                    xb[r] = make_double2(digit_to_double<BGBIT>(dv[r], shift - BGBIT), digit_to_double<BGBIT>(dv[r + 8], shift - BGBIT));
+                fft.forward2(xa, xb, bufs, bufs + kBuf, bar);
+                mac_event(ev, xa, &xb, q * L + p);
+            } else {
+                fft.forward(xa, bufs, bar);
+                mac_event(ev, xa, nullptr, q * L + p);
+            }
+        }
+    }
+    bar();
+    fft.template inverse2<true>(acc0, acc1, bufs, bufs + kBuf, bar);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const int j = t + 64 * r;
+        const double sc = c_tw.p1_scale[r];   // 1/512 times the cos factors the last pass left out
+        const int32_t lo0 = round_scaled_to_torus(acc0[r].x, sc), hi0 = round_scaled_to_torus(acc0[r].y, sc);
+        const int32_t lo1 = round_scaled_to_torus(acc1[r].x, sc), hi1 = round_scaled_to_torus(acc1[r].y, sc);
+        if (MODE == 0) { ACC[j] += lo0; ACC[j + kM] += hi0; ACC[kN + j] += lo1; ACC[kN + j + kM] += hi1; }
+        else           { ACC[j] = lo0;  ACC[j + kM] = hi0;  ACC[kN + j] = lo1;  ACC[kN + j + kM] = hi1; }
+    }
+    bar();  // accumulator complete before the next step's rotated reads; exchange buffers free
+}
+template <int L, int BGBIT, int MODE, class Barrier, class Rows>
+__device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int a, const Rows &rows,
+                                          const FftTmAcc &fft, const Barrier &bar) {
+    cmux_step_pairs_tmacc<L, BGBIT, MODE>(ACC, bufs, a, rows, fft, bar);
+}
+
 // per ciphertext group: ACC + 2 exchange buffers + bara
-constexpr int kGroupSmemBytes = 2 * kN * 4 + 2 * kBufElems * 16 + 1280;
+template <class FFT> __host__ __device__ constexpr int group_smem_bytes() { return 2 * kN * 4 + 2 * FFT::kBufElemsPerTransform * 16 + 1280; }
+constexpr int kGroupSmemBytes = 2 * kN * 4 + 2 * kBufElems * 16 + 1280;   // FftSmem (also the experiments' kernels)
 constexpr int kBrStages = 4;
-constexpr int br_smem_bytes(int groups, int stages = kBrStages) { return groups * kGroupSmemBytes + stages * kStageBytes + 128; }
-constexpr int kCmuxTestSmemBytes = kGroupSmemBytes;
+template <class FFT> __host__ __device__ constexpr int br_smem_bytes(int groups, int stages) {
+    return groups * group_smem_bytes<FFT>() + stages * kStageBytes + 128;
+}
 
 #ifndef BR_MAXREG
 #define BR_MAXREG 255
 #endif
 // G ciphertexts per CTA (64 threads each), walking i = 0..n-1 in lockstep on one TMA-fed ring of
 // bootstrapping-key row pairs.  Groups synchronise among themselves with named barriers only.
-template <int L, int BGBIT, int G, int STAGES = kBrStages>
+// FFT = FftSmem: both exchanges of a transform through shared memory (round 1, "v2");
+//       FftTm:   the two warp-local exchanges and the per-thread roots in tensor memory ("tm", negacyclic_fft_tm.cuh).
+template <int L, int BGBIT, int G, int STAGES, class FFT>
 __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key, const BlindRotateArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr int KPL = 2 * L;
     unsigned char *ring = smem;                                                       // [stages][16 KiB]
     RingState<STAGES> *st = reinterpret_cast<RingState<STAGES> *>(smem + STAGES * kStageBytes);
     const int g = threadIdx.x >> 6, t = threadIdx.x & 63;
-    unsigned char *mine = smem + STAGES * kStageBytes + 128 + (size_t)g * kGroupSmemBytes;
+    unsigned char *mine = smem + STAGES * kStageBytes + 128 + (size_t)g * group_smem_bytes<FFT>();
     int32_t *ACC = reinterpret_cast<int32_t *>(mine);                                // [2][1024]
-    double2 *bufs = reinterpret_cast<double2 *>(mine + 2 * kN * 4);                  // [2][576]
-    uint16_t *bara = reinterpret_cast<uint16_t *>(mine + 2 * kN * 4 + 2 * kBufElems * 16);  // [n+1]
+    double2 *bufs = reinterpret_cast<double2 *>(mine + 2 * kN * 4);                  // [2][576 | 512]
+    uint16_t *bara = reinterpret_cast<uint16_t *>(mine + 2 * kN * 4 + 2 * FFT::kBufElemsPerTransform * 16);  // [n+1]
+    const double2 *bkfft = UsesTm<FFT>::value ? key.bkfft_tm : key.bkfft;
+    uint32_t *tm_slot_p = reinterpret_cast<uint32_t *>(smem + STAGES * kStageBytes + 120);   // behind the ring state
+    uint32_t tm = 0;
+    static_assert(!UsesTm<FFT>::value || ((2 * G + 3) / 4) * TmWindow<FFT>::value <= 512, "tensor-memory columns of the warps sharing a lane quarter");
+    if (UsesTm<FFT>::value) tm = tm_alloc_cta(tm_slot_p, TmWindow<FFT>::value);
 
     const int n = key.n, n1 = n + 1;
     const int bmin = min((int)blockIdx.x, a.bal_r);
@@ -347,7 +629,7 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         for (int s = 0; s < STAGES && s < total; ++s)
-            tma_load_row_pair(ring + (size_t)s * kStageBytes, key.bkfft + (size_t)s * 2 * kM, &st->full[s]);
+            tma_load_row_pair(ring + (size_t)s * kStageBytes, bkfft + (size_t)s * 2 * kM, &st->full[s]);
     }
 
     // ---- gate prologue + modulus switch to 2N (numeric-functions.cpp:59-65)
@@ -388,18 +670,19 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
             ACC[kN + j] = ((j + barb) & kN) ? -mu : mu;
         }
     }
-    const RootSet w2 = load_rootset(c_tw.p2[t >> 3]), w3 = load_rootset(c_tw.p3[t]);
+    FFT fft;
+    fft.init(t, tm);
     const NamedBarrier64 bar{1 + g};
     bar();
 
     // ---- blind rotation (lwe-bootstrapping-functions-fft.cpp:88-112)
-    RingRows<STAGES> rows{ring, st, key.bkfft, 0, total, 2 * G};
+    RingRows<STAGES> rows{ring, st, bkfft, 0, total, 2 * G};
 #pragma unroll 1
     for (int i = 0; i < n; ++i) {
         rows.seq0 = i * KPL;
         const int ai = live ? bara[i] : 0;
         if (ai == 0) { rows.skip_step(KPL); continue; }
-        cmux_step<L, BGBIT, 0>(ACC, bufs, ai, rows, t, w2, w3, bar);
+        cmux_step<L, BGBIT, 0>(ACC, bufs, ai, rows, fft, bar);
     }
 
     // ---- sample extract at index 0 (lwe.cpp:41-60)
@@ -412,6 +695,7 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
         }
         if (t == 0) u[kN] = ACC[kN];
     }
+    if (UsesTm<FFT>::value) tm_free_cta(tm_slot_p);
 }
 
 }  // namespace b200
@@ -424,24 +708,35 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
 #include "blind_rotate_lat.cuh"
 namespace b200 {
 
-template <int L, int BGBIT>
-__global__ void __launch_bounds__(64, 6) k_cmux_test(const DeviceKey key, int32_t *acc, int bk_index, int barai, int mode) {
+// FftSmem: several CTAs per SM; FftTm: one CTA per SM owns the tensor memory (512 columns), so the CTA walks a slice
+// of the accumulators
+template <int L, int BGBIT, class FFT>
+__global__ void __launch_bounds__(64, UsesTm<FFT>::value ? 1 : 6) k_cmux_test(const DeviceKey key, int32_t *acc, int bk_index,
+                                                                            int barai, int mode, int64_t count) {
     extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ uint32_t tm_slot_s;
     int32_t *ACC = reinterpret_cast<int32_t *>(smem);
     double2 *bufs = reinterpret_cast<double2 *>(smem + 2 * kN * 4);
     const int t = threadIdx.x;
-    int32_t *g = acc + (size_t)blockIdx.x * 2 * kN;
-    for (int j = t; j < 2 * kN; j += 64) ACC[j] = g[j];
-    const RootSet w2 = load_rootset(c_tw.p2[t >> 3]), w3 = load_rootset(c_tw.p3[t]);
-    __syncthreads();
-    const GlobalRows rows{key.bkfft + (size_t)bk_index * (2 * L * 2 * kM)};
-    if (mode == 0) {
-        if (barai != 0) cmux_step<L, BGBIT, 0>(ACC, bufs, barai, rows, t, w2, w3, CtaBarrier());
-    } else {
-        cmux_step<L, BGBIT, 1>(ACC, bufs, 0, rows, t, w2, w3, CtaBarrier());
+    uint32_t tm = 0;
+    if (UsesTm<FFT>::value) tm = tm_alloc_cta(&tm_slot_s);
+    FFT fft;
+    fft.init(t, tm);
+    const GlobalRows rows{(UsesTm<FFT>::value ? key.bkfft_tm : key.bkfft) + (size_t)bk_index * (2 * L * 2 * kM)};
+    for (int64_t item = blockIdx.x; item < count; item += gridDim.x) {
+        int32_t *g = acc + (size_t)item * 2 * kN;
+        for (int j = t; j < 2 * kN; j += 64) ACC[j] = g[j];
+        __syncthreads();
+        if (mode == 0) {
+            if (barai != 0) cmux_step<L, BGBIT, 0>(ACC, bufs, barai, rows, fft, CtaBarrier());
+        } else {
+            cmux_step<L, BGBIT, 1>(ACC, bufs, 0, rows, fft, CtaBarrier());
+        }
+        __syncthreads();
+        for (int j = t; j < 2 * kN; j += 64) g[j] = ACC[j];
+        __syncthreads();
     }
-    __syncthreads();
-    for (int j = t; j < 2 * kN; j += 64) g[j] = ACC[j];
+    if (UsesTm<FFT>::value) tm_free_cta(&tm_slot_s);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -605,21 +900,28 @@ __global__ void k_linear_desc(int32_t *pool, const int32_t *desc, int n1) {
         else return cudaErrorInvalidValue;                                          \
     } while (0)
 
-template <int L, int BGBIT, int G>
+template <int L, int BGBIT, class FFT>
 static cudaError_t set_br_attr() {
     static bool done[16] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 16 && done[dev]) return cudaSuccess;
-    cudaError_t e = cudaFuncSetAttribute(k_cmux_test<L, BGBIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCmuxTestSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(k_cmux_test<L, BGBIT, FFT>, cudaFuncAttributeMaxDynamicSharedMemorySize, group_smem_bytes<FFT>());
     if (e != cudaSuccess) return e;
     if (dev < 16) done[dev] = true;
     return cudaSuccess;
 }
 
+static int sm_count_of(int dev);
 cudaError_t launch_bk_convert(const DeviceKey &key, const int32_t *d_bk_coefs, cudaStream_t s) {
     const int polys = key.n * (key.k + 1) * key.l * (key.k + 1);
-    k_bk_convert<<<polys, 64, 0, s>>>(d_bk_coefs, key.bkfft);
+    k_bk_convert<FftSmem><<<polys, 64, 0, s>>>(d_bk_coefs, key.bkfft, polys);
+    COUNT_LAUNCH();
+    // the tensor-memory transform has its own evaluation order, hence its own copy of the key; a CTA of that
+    // kernel owns an SM's tensor memory, so the grid is a few CTAs per SM walking the polynomials
+    int dev = 0;
+    cudaGetDevice(&dev);
+    k_bk_convert<FftTm><<<sm_count_of(dev) * 4, 64, 0, s>>>(d_bk_coefs, key.bkfft_tm, polys);
     COUNT_LAUNCH();
 #ifdef B200_EXPERIMENTS
     k_bk_convert16<<<polys, 32, 0, s>>>(d_bk_coefs, key.bkfft16);
@@ -651,15 +953,17 @@ static bool br_balance() {
     static const bool on = [] { const char *e = getenv("B200_BALANCE"); return !(e && e[0] == '0'); }();
     return on;
 }
-template <int L, int BGBIT, int G, int STAGES>
+template <int L, int BGBIT, int G, int STAGES, class FFT = FftSmem>
 static cudaError_t br_launch_st(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
     static bool done[16] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
+    constexpr int smem_bytes = br_smem_bytes<FFT>(G, STAGES);
+    static_assert(smem_bytes <= 227 * 1024, "shared memory budget of one CTA");
     if (!(dev < 16 && done[dev])) {
-        cudaError_t e = cudaFuncSetAttribute(k_blind_rotate<L, BGBIT, G, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, br_smem_bytes(G, STAGES));
+        cudaError_t e = cudaFuncSetAttribute(k_blind_rotate<L, BGBIT, G, STAGES, FFT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
         if (e != cudaSuccess) return e;
-        cudaFuncSetAttribute(k_blind_rotate<L, BGBIT, G, STAGES>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(k_blind_rotate<L, BGBIT, G, STAGES, FFT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         if (dev < 16) done[dev] = true;
     }
     unsigned grid = (unsigned)((a.items + G - 1) / G);
@@ -675,7 +979,7 @@ static cudaError_t br_launch_st(const DeviceKey &key, const BlindRotateArgs &a, 
             b.bal_r = (int)(a.items % even);
         }
     }
-    k_blind_rotate<L, BGBIT, G, STAGES><<<grid, 64 * G, br_smem_bytes(G, STAGES), s>>>(key, b);
+    k_blind_rotate<L, BGBIT, G, STAGES, FFT><<<grid, 64 * G, smem_bytes, s>>>(key, b);
     return cudaSuccess;
 }
 // Ring depth: 3 stages for the 6-ciphertext CTA, 7 for the 4-ciphertext CTA (everything that fits in 227 KB),
@@ -685,6 +989,13 @@ static cudaError_t br_launch(const DeviceKey &key, const BlindRotateArgs &a, cud
     if constexpr (G == 6) return br_launch_st<L, BGBIT, G, 3>(key, a, s);
     else if constexpr (G == 4) return br_launch_st<L, BGBIT, G, 7>(key, a, s);
     else return br_launch_st<L, BGBIT, G, 2>(key, a, s);
+}
+// the tensor-memory transform needs 25.9 KB per group instead of 27.9: one more ring stage with six groups
+template <int L, int BGBIT, int G, class FFT = FftTm>
+static cudaError_t br_launch_tm(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
+    if constexpr (G == 6) return br_launch_st<L, BGBIT, G, 4, FFT>(key, a, s);
+    else if constexpr (G == 5) return br_launch_st<L, BGBIT, G, 6, FFT>(key, a, s);
+    else return br_launch_st<L, BGBIT, G, 7, FFT>(key, a, s);
 }
 // Kernel choice: 0 = 64 threads per ciphertext (default), 1 = warp per ciphertext with TMEM accumulators
 // (B200_BR_KERNEL=w16 or b200_set_blind_rotate_kernel(1)).
@@ -796,6 +1107,34 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         return cudaGetLastError();
     }
 #endif
+    if (br_variant() == 10 && a.items > 148 * 4) {
+        // "tmacc": the tm kernel with the spectral accumulators parked in tensor memory between row pairs
+        cudaError_t et;
+        static int tmg = -1;
+        if (tmg < 0) { const char *ev = getenv("B200_TM_G"); tmg = ev ? atoi(ev) : 6; }
+        if (key.l == 2 && key.Bgbit == 10 && tmg == 4) et = br_launch_tm<2, 10, 4, FftTmAcc>(key, a, s);
+        else if (key.l == 2 && key.Bgbit == 10) et = br_launch_tm<2, 10, 6, FftTmAcc>(key, a, s);
+        else if (key.l == 3 && key.Bgbit == 7) et = br_launch_tm<3, 7, 6, FftTmAcc>(key, a, s);
+        else return cudaErrorInvalidValue;
+        if (et != cudaSuccess) return et;
+        COUNT_LAUNCH();
+        return cudaGetLastError();
+    }
+    if (br_variant() == 9 && a.items > 148 * 4) {
+        // "tm": the warp-local exchanges of every transform and the per-thread roots in tensor memory
+        cudaError_t et;
+        static int tmg = -1;   // ciphertexts per CTA at l = 2 (A/B knob: B200_TM_G=4|5|6)
+        if (tmg < 0) { const char *ev = getenv("B200_TM_G"); tmg = ev ? atoi(ev) : 6; }
+        if (key.l == 2 && key.Bgbit == 10 && tmg == 5) et = br_launch_tm<2, 10, 5>(key, a, s);
+        else if (key.l == 2 && key.Bgbit == 10 && tmg == 4) et = br_launch_tm<2, 10, 4>(key, a, s);
+        else if (key.l == 2 && key.Bgbit == 10) et = br_launch_tm<2, 10, 6>(key, a, s);
+        else if (key.l == 3 && key.Bgbit == 7) et = br_launch_tm<3, 7, 4>(key, a, s);
+        else if (key.l == 2 && key.Bgbit == 8) et = br_launch_tm<2, 8, 6>(key, a, s);
+        else return cudaErrorInvalidValue;
+        if (et != cudaSuccess) return et;
+        COUNT_LAUNCH();
+        return cudaGetLastError();
+    }
     // More than one ciphertext per SM: multi-ciphertext CTAs on a balanced grid (br_launch_st).  Measured at
     // l = 2 (ms, G=1 x 3 CTAs per SM / G=4 / G=6): 296 items 2.39 / 2.29 / 2.66; 591: 4.69 / 3.44 / 3.73;
     // 600: - / 5.49 / 4.74; 887: - / 6.48 / 4.92.
@@ -867,11 +1206,29 @@ cudaError_t launch_cmux_test(const DeviceKey &key, int32_t *d_acc, int bk_index,
         return cudaGetLastError();
     }
 #endif
+    if (br_variant() == 9 || br_variant() == 10) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        const unsigned grid = (unsigned)std::min<int64_t>(count, sm_count_of(dev));
+#define CTT_LAUNCH(L_, B_)                                                                \
+    do {                                                                                  \
+        cudaError_t e = set_br_attr<L_, B_, FftTm>();                                     \
+        if (e != cudaSuccess) return e;                                                   \
+        k_cmux_test<L_, B_, FftTm><<<grid, 64, group_smem_bytes<FftTm>(), s>>>(key, d_acc, bk_index, barai, mode, count); \
+    } while (0)
+        if (key.l == 2 && key.Bgbit == 10) CTT_LAUNCH(2, 10);
+        else if (key.l == 3 && key.Bgbit == 7) CTT_LAUNCH(3, 7);
+        else if (key.l == 2 && key.Bgbit == 8) CTT_LAUNCH(2, 8);
+        else return cudaErrorInvalidValue;
+#undef CTT_LAUNCH
+        COUNT_LAUNCH();
+        return cudaGetLastError();
+    }
 #define CT_LAUNCH(L_, B_)                                                                 \
     do {                                                                                  \
-        cudaError_t e = set_br_attr<L_, B_, 1>();                                         \
+        cudaError_t e = set_br_attr<L_, B_, FftSmem>();                                   \
         if (e != cudaSuccess) return e;                                                   \
-        k_cmux_test<L_, B_><<<(unsigned)count, 64, kCmuxTestSmemBytes, s>>>(key, d_acc, bk_index, barai, mode); \
+        k_cmux_test<L_, B_, FftSmem><<<(unsigned)count, 64, group_smem_bytes<FftSmem>(), s>>>(key, d_acc, bk_index, barai, mode, count); \
     } while (0)
     if (key.l == 2 && key.Bgbit == 10) CT_LAUNCH(2, 10);
     else if (key.l == 3 && key.Bgbit == 7) CT_LAUNCH(3, 7);

@@ -236,6 +236,35 @@ __global__ void __launch_bounds__(THREADS, 1) k_tmem(int mode, double *sink, lon
 #pragma unroll
             for (int r = 0; r < 16; ++r) { v[r] = w0[r] + 1; v[16 + r] = w1[r] + 1; }
         }
+        else if (m == 6) {
+            // the same exchange with the narrowest forms: 16 x st 32x32b.x2 (one double each), 8 x ld 16x256b.x1
+#pragma unroll
+            for (int d = 0; d < 16; ++d)
+                asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1,%2};" ::"r"(taddr + 2 * d), "r"(v[2 * d]), "r"(v[2 * d + 1]) : "memory");
+            tm_wait_st();
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                asm volatile("tcgen05.ld.sync.aligned.16x256b.x1.b32 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(v[4 * q]), "=r"(v[4 * q + 1]), "=r"(v[4 * q + 2]), "=r"(v[4 * q + 3])
+                             : "r"(taddr + 8 * (q & 3) + ((uint32_t)(16 * (q >> 2)) << 16)) : "memory");
+            tm_wait_ld();
+#pragma unroll
+            for (int r = 0; r < 32; ++r) v[r] += 1;
+        } else if (m == 7) {
+            // st 32x32b.x4 x 8 (a double2 each), ld 16x256b.x2 x 4
+#pragma unroll
+            for (int d = 0; d < 8; ++d)
+                asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1,%2,%3,%4};" ::"r"(taddr + 4 * d), "r"(v[4 * d]), "r"(v[4 * d + 1]), "r"(v[4 * d + 2]), "r"(v[4 * d + 3]) : "memory");
+            tm_wait_st();
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                asm volatile("tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                             : "=r"(v[8 * q]), "=r"(v[8 * q + 1]), "=r"(v[8 * q + 2]), "=r"(v[8 * q + 3]), "=r"(v[8 * q + 4]), "=r"(v[8 * q + 5]), "=r"(v[8 * q + 6]), "=r"(v[8 * q + 7])
+                             : "r"(taddr + 16 * (q & 1) + ((uint32_t)(16 * (q >> 1)) << 16)) : "memory");
+            tm_wait_ld();
+#pragma unroll
+            for (int r = 0; r < 32; ++r) v[r] += 1;
+        }
         if (mode & 16) {
 #pragma unroll
             for (int r = 0; r < 8; ++r) buf[t + THREADS * r] = y[r];
@@ -356,6 +385,9 @@ int main(int argc, char **argv) {
             run(k_tmem<T>, T, 3, smem, "TMEM st 32x32b.x32 x4 (512 B/thread)", sink, cyc); \
             run(k_tmem<T>, T, 4, smem, "TMEM st 16x256b.x8 x4 (512 B/thread)", sink, cyc); \
             run(k_tmem<T>, T, 5, smem, "TMEM exchange st 32x32b.x32 -> 2 ld 16x256b.x4 (128 B each way)", sink, cyc); \
+            run(k_tmem<T>, T, 6, smem, "TMEM exchange 16 st 32x32b.x2 -> 8 ld 16x256b.x1", sink, cyc); \
+            run(k_tmem<T>, T, 7, smem, "TMEM exchange 8 st 32x32b.x4 -> 4 ld 16x256b.x2", sink, cyc); \
+            run(k_tmem<T>, T, 6 + 32, smem, "TMEM exchange (narrow) + 96 DFMA", sink, cyc); \
             run(k_tmem<T>, T, 16, smem, "smem exchange 8 STS.128 + 8 LDS.128 (128 B each way)", sink, cyc); \
             run(k_tmem<T>, T, 32, smem, "96 DFMA", sink, cyc); \
             run(k_tmem<T>, T, 5 + 16, smem, "TMEM exchange + smem exchange", sink, cyc); \

@@ -15,12 +15,12 @@ pytestmark = [pytest.mark.gpu,
 
 # every parity check runs against both blind-rotation kernels (64 threads per ciphertext / warp per
 # ciphertext with TMEM accumulators)
-@pytest.fixture(scope="module", params=[(80, "v2"), (128, "v2"), (80, "w16"), (128, "w16")],
-                ids=["P80-v2", "P128-v2", "P80-w16", "P128-w16"])
+@pytest.fixture(scope="module", params=[(80, "v2"), (128, "v2"), (80, "tm"), (128, "tm"), (80, "w16"), (128, "w16")],
+                ids=["P80-v2", "P128-v2", "P80-tm", "P128-tm", "P80-w16", "P128-w16"])
 def keys(request):
     from eoc_tfhe_b200 import CloudKey, set_blind_rotate_kernel, experiments_built
     lam, kernel = request.param
-    if kernel != "v2" and not experiments_built():
+    if kernel not in ("v2", "tm") and not experiments_built():
         pytest.skip("round-1 variant: built only with B200_EXPERIMENTS=1")
     set_blind_rotate_kernel(kernel)
     ref = reflib.RefLib()

@@ -256,6 +256,39 @@ def test_dropin_symbols_on_libtfhe_samples(p80):
     rk.L.delete_LweSample_array(4, s)
 
 
+def test_tm_blind_rotation_bit_identical(p80):
+    """The blind rotation whose warp-local exchanges and roots live in tensor memory ("tm", negacyclic_fft_tm.cuh)
+    against the shared-memory kernel ("v2") on a wide batch with a ragged tail, an all-zero input and a
+    half-zero input: same extracted samples word for word (every external product is an exact integer
+    convolution far inside the FP64 rounding margin), at both parameter sets; then gates through it decrypt."""
+    from eoc_tfhe_b200 import CloudKey, GateOp, set_blind_rotate_kernel
+    rk, ck = p80
+    rng = np.random.default_rng(78)
+    try:
+        for lam in (80, 128):
+            if lam == 80:
+                rkk, ckk = rk, ck
+            else:
+                rkk = reflib.RefLib().keygen(128, seed=4321)
+                ckk = CloudKey.from_libtfhe(rkk.cloud_ptr)
+            x = rng.integers(-2**31, 2**31, size=(148 * 6 + 13, rkk.n + 1), dtype=np.int64).astype(np.int32)
+            x[7] = 0
+            x[8, :200] = 0
+            set_blind_rotate_kernel("v2")
+            want = ckk.bootstrap_woks(x)
+            set_blind_rotate_kernel("tm")
+            got = ckk.bootstrap_woks(x)
+            assert np.array_equal(got, want), lam
+            if lam == 128:
+                ckk.close()
+        bits = rng.integers(0, 2, size=64).astype(np.int32)
+        cts = rk.encrypt_bits(bits)
+        out = ck.gate(GateOp.NAND, np.tile(cts, (15, 1)), np.tile(cts, (15, 1)))
+        assert np.array_equal(rk.decrypt_bits(out), np.tile(1 - bits, 15))
+    finally:
+        set_blind_rotate_kernel("v2")
+
+
 def test_tensor_memory_blind_rotation_variants_bit_identical(p80):
     """The experimental blind-rotation kernels (accumulators in tensor memory: 6 groups per SM / two ciphertexts
     per group sharing every key read; key delivered through tensor memory by tcgen05.cp; two warps per
