@@ -47,7 +47,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--gates", type=int, default=GATES_PER_GPU, help="gates per GPU per step (default: the BASELINE config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--kernel", default=None, choices=["v2", "w16"], help="blind-rotation kernel (default: the library's)")
+    ap.add_argument("--kernel", default=None, choices=["auto", "v2", "tm", "tmacc", "tms", "w16"], help="blind-rotation kernel (default: the library's)")
     return ap.parse_args()
 
 

@@ -66,7 +66,7 @@ extern "C" int b200_set_device(int device) {
 }
 extern "C" int64_t b200_launch_count(void) { return launch_count(); }
 extern "C" int b200_set_blind_rotate_kernel(int variant) {
-    if (variant < 0 || variant > 10) return b200_fail("blind-rotation kernel variant must be 0..10");
+    if (variant < 0 || variant > 12) return b200_fail("blind-rotation kernel variant must be 0..12");
     if (variant != 0 && variant < 9 && !experiments_built())
         return b200_fail("blind-rotation variants 1..8 are round-1 experiments: rebuild with -DB200_EXPERIMENTS");
     set_blind_rotate_variant(variant);

@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(32 * G, 1) k_blind_rotate16(const DeviceKey ke
     __syncwarp();
 
     // ---- blind rotation (lwe-bootstrapping-functions-fft.cpp:88-112)
-    RingRows<kBr16Stages> rows{ring, st, key.bkfft16, 0, total, G};
+    RingRows<kBr16Stages> rows{ring, st, key.bkfft16, 0, total, G, (threadIdx.x & 31) == 0};
 #pragma unroll 1
     for (int i = 0; i < n; ++i) {
         rows.seq0 = i * KPL;

@@ -306,7 +306,7 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate3(const DeviceKey key
     bar();
 
     // ---- blind rotation (lwe-bootstrapping-functions-fft.cpp:88-112)
-    RingRows<STAGES> rows{ring, st, key.bkfft, 0, total, 2 * G};
+    RingRows<STAGES> rows{ring, st, key.bkfft, 0, total, 2 * G, (threadIdx.x & 31) == 0};
 #pragma unroll 1
     for (int i = 0; i < n; ++i) {
         rows.seq0 = i * KPL;

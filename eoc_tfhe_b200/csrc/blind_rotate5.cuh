@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate5(const DeviceKey key
     bar();
 
     // ---- blind rotation (lwe-bootstrapping-functions-fft.cpp:88-112): a row pair is read by one warp per group
-    RingRows<kV5Stages> rows{ring, st, key.bkfft16, 0, total, G};
+    RingRows<kV5Stages> rows{ring, st, key.bkfft16, 0, total, G, (threadIdx.x & 31) == 0};
 #pragma unroll 1
     for (int i = 0; i < n; ++i) {
         rows.seq0 = i * KPL;

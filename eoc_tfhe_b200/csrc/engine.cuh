@@ -44,6 +44,7 @@ struct BlindRotateArgs {
     // balanced grid of the multi-ciphertext CTA (set by the launcher): CTA b owns bal_q + (b < bal_r)
     // consecutive items; bal_q == 0: CTA b owns items [b*G, b*G + G)
     int bal_q = 0, bal_r = 0;
+    int stagger = 0;          // clk: groups that share warp schedulers start (g >> 1) * stagger apart (A/B knob)
 };
 constexpr int kOpRaw = 100;
 

@@ -120,7 +120,7 @@ cudaError_t upload_twiddles() {
 // ------------------------------------------------------------------------------------------------
 // tensor memory of a CTA: all 512 columns, allocated by warp 0; every warp gets a 128-column window in its own lane
 // quarter (a warp reaches lanes 32 (warp % 4) .. +31 only); warps that share a quarter get different columns
-__device__ __forceinline__ uint32_t tm_alloc_cta(uint32_t *slot, const int window = kTmColsPerWarp) {
+__device__ __forceinline__ uint32_t tm_alloc_cta(uint32_t *slot, const int window = kTmColsPerWarp, const int shared = 0) {
     if (threadIdx.x < 32) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((uint32_t)__cvta_generic_to_shared(slot)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -129,7 +129,7 @@ __device__ __forceinline__ uint32_t tm_alloc_cta(uint32_t *slot, const int windo
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t warp = threadIdx.x >> 5;
-    return *slot + (((warp & 3u) * 32u) << 16) + (warp >> 2) * (uint32_t)window;
+    return *slot + (((warp & 3u) * 32u) << 16) + (uint32_t)shared + (warp >> 2) * (uint32_t)window;
 }
 __device__ __forceinline__ void tm_free_cta(const uint32_t *slot) {
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -139,8 +139,14 @@ __device__ __forceinline__ void tm_free_cta(const uint32_t *slot) {
 template <class FFT> struct UsesTm { static constexpr bool value = false; };
 template <> struct UsesTm<FftTm> { static constexpr bool value = true; };
 template <> struct UsesTm<FftTmAcc> { static constexpr bool value = true; };
+template <> struct UsesTm<FftTmS> { static constexpr bool value = true; };
+template <class FFT> struct PairEvents { static constexpr bool value = false; };   // ring released per MAC event (release_n)
+template <> struct PairEvents<FftTmAcc> { static constexpr bool value = true; };
 template <class FFT> struct TmWindow { static constexpr int value = kTmColsPerWarp; };
 template <> struct TmWindow<FftTmAcc> { static constexpr int value = kTmColsPerWarpAcc; };
+template <> struct TmWindow<FftTmS> { static constexpr int value = kTmSColsPerWarp; };
+template <class FFT> struct TmShared { static constexpr int value = 0; };       // columns shared by a lane quarter
+template <> struct TmShared<FftTmS> { static constexpr int value = kTmSColsRoots; };
 
 template <class FFT>
 __global__ void __launch_bounds__(64) k_bk_convert(const int32_t *__restrict__ coefs, double2 *__restrict__ out, int polys) {
@@ -219,6 +225,9 @@ struct GlobalRows {
     __device__ __forceinline__ const double2 *acquire(int rp) const { return bk_i + (size_t)rp * 2 * kM; }
     __device__ __forceinline__ double2 load(const double2 *p) const { return __ldg(p); }
     __device__ __forceinline__ void release(int) const {}
+    __device__ __forceinline__ int release_begin(int) const { return 0; }
+    __device__ __forceinline__ void release_end(int, int) const {}
+    __device__ __forceinline__ void release_n(int, int) const {}
 };
 
 constexpr int kStageBytes = 2 * kM * 16;  // one row pair
@@ -260,6 +269,7 @@ struct RingRows {
     int seq0;                      // sequence number of row pair 0 of the current CMux step (= i * kpl)
     int total;                     // n * kpl
     int warps;                     // consumer warps per CTA
+    bool lane0;                    // this thread does the warp's ring bookkeeping
     __device__ __forceinline__ const double2 *acquire(int rp) const {
         const int q = seq0 + rp;
         mbar_wait(&st->full[q % STAGES], (uint32_t)(q / STAGES) & 1u);
@@ -270,7 +280,7 @@ struct RingRows {
     __device__ __forceinline__ void release(int rp) const {
         const int q = seq0 + rp, s = q % STAGES;
         __syncwarp();
-        if ((threadIdx.x & 31) == 0) {
+        if (lane0) {
             __threadfence_block();
             if (atomicAdd(&st->done[s], 1) == warps - 1) {
                 st->done[s] = 0;
@@ -279,9 +289,55 @@ struct RingRows {
             }
         }
     }
+    // n consecutive row pairs that every warp consumes together (the pair-wise CMux step): ONE count for all of
+    // them -- the counter of the first -- and the last warp refills the n stages
+    __device__ __forceinline__ void release_n(int rp, int n) const {
+        const int q = seq0 + rp, s = q % STAGES;
+        __syncwarp();
+        if (lane0) {
+            __threadfence_block();
+            if (atomicAdd(&st->done[s], 1) == warps - 1) {
+                st->done[s] = 0;
+                for (int i = 0; i < n; ++i)
+                    if (q + i + STAGES < total)
+                        tma_load_row_pair(ring + (size_t)((q + i) % STAGES) * kStageBytes, bk + (size_t)(q + i + STAGES) * 2 * kM,
+                                          &st->full[(q + i) % STAGES]);
+            }
+        }
+    }
+    // The same in two halves, so that the shared-memory atomic's round trip (lane 0 needs the old count to know
+    // whether it is the last warp; the whole warp waits for lane 0 at the reconvergence point) overlaps with the
+    // caller's next piece of work: release_begin issues the atomic, release_end looks at its result.
+    __device__ __forceinline__ int release_begin(int rp) const {
+        const int q = seq0 + rp, s = q % STAGES;
+        int old = -1;
+        __syncwarp();
+        if (lane0) {
+            __threadfence_block();
+            old = atomicAdd(&st->done[s], 1);
+        }
+        return old;
+    }
+    __device__ __forceinline__ void release_end(int rp, int old) const {
+        const int q = seq0 + rp, s = q % STAGES;
+        if (lane0 && old == warps - 1) {
+            st->done[s] = 0;
+            if (q + STAGES < total)
+                tma_load_row_pair(ring + (size_t)s * kStageBytes, bk + (size_t)(q + STAGES) * 2 * kM, &st->full[s]);
+        }
+    }
     // a group that does nothing this step (barai == 0, or no ciphertext) still has to hand the stages on
     __device__ __forceinline__ void skip_step(int kpl) const {
         for (int rp = 0; rp < kpl; ++rp) { acquire(rp); release(rp); }
+    }
+    // the same in the event structure of the pair-wise step (release_n): digits (p, p+1) of each polynomial together
+    __device__ __forceinline__ void skip_step_pairs(int l) const {
+        for (int q = 0; q < 2; ++q)
+            for (int p = 0; p < l; p += 2) {
+                const int n = p + 1 < l ? 2 : 1, rp = q * l + p;
+                for (int i = 0; i < n; ++i) acquire(rp + i);
+                release_n(rp, n);
+            }
     }
 };
 
@@ -498,7 +554,8 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
             c1[i].y = fma(x[r].y, b1.x, c1[i].y);
         }
     };
-    // event ev over rows rp (and rp + 1 when xb is given)
+    // MAC event ev over rows rp (and rp + 1 when xb is given): acc (tensor memory, or zero for the first event)
+    // += x . rows; the last event of the step leaves the result in acc0 / acc1.  Half of the registers at a time.
     auto mac_event = [&](const int ev, const double2 (&xa)[8], const double2 (*xb)[8], const int rp) {
         const double2 *rowa = rows.acquire(rp) + t;
         const double2 *rowb = xb ? rows.acquire(rp + 1) + t : nullptr;
@@ -525,8 +582,7 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
                            c0[2].x, c0[2].y, c1[2].x, c1[2].y, c0[3].x, c0[3].y, c1[3].x, c1[3].y);
             }
         }
-        rows.release(rp);
-        if (xb) rows.release(rp + 1);
+        rows.release_n(rp, xb ? 2 : 1);
     };
 
 #pragma unroll
@@ -586,8 +642,119 @@ __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int
     cmux_step_pairs_tmacc<L, BGBIT, MODE>(ACC, bufs, a, rows, fft, bar);
 }
 
+// Single transforms with the spectral accumulators in tensor memory across EVERY key row (FftTmS): per row the two
+// halves of the accumulators are loaded (not for the first row), updated and stored; the inverse transforms load
+// one output column at a time.  About 100 live registers, one exchange buffer: eight groups per SM.
+template <int L, int BGBIT, int MODE, class Barrier, class Rows>
+__device__ __forceinline__ void cmux_step_single_tmacc(int32_t *ACC, double2 *buf, const int a, const Rows &rows,
+                                                       const FftTmS &fft, const Barrier &bar) {
+    constexpr uint32_t BG = 1u << BGBIT, HALF = BG >> 1;
+    const int t = fft.t;
+    const uint32_t tm_acc = fft.tm + kTmSColAcc;     // per half h: [c0 x 4 | c1 x 4] = 32 columns
+    uint32_t offset = 0;  // tgsw.cpp:7-29
+#pragma unroll
+    for (int p = 0; p < L; ++p) offset += HALF << (32 - (p + 1) * BGBIT);
+
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        const int32_t *P = ACC + q * kN;
+        uint32_t dv[16];  // (rotated difference) + decomposition offset, coefficient t + 64 rr
+#pragma unroll
+        for (int rr = 0; rr < 16; ++rr) {
+            const int j = t + 64 * rr;
+            if (MODE == 0) {
+                const int m = (j - a) & (2 * kN - 1);
+                int32_t v = P[m & (kN - 1)];
+                if (m & kN) v = -v;
+                dv[rr] = (uint32_t)(v - P[j]) + offset;
+            } else {
+                dv[rr] = (uint32_t)P[j] + offset;
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < L; ++p) {
+            const int ev = q * L + p;
+            if (ev > 0) bar();   // the partner warp has read the previous transform's exchange buffer
+            const int shift = 32 - (p + 1) * BGBIT;
+            double2 x[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+                x[r] = make_double2(digit_to_double<BGBIT>(dv[r], shift), digit_to_double<BGBIT>(dv[r + 8], shift));
+            fft.forward(x, buf, bar);
+            const double2 *row = rows.acquire(ev) + t;
+            if (ev > 0) tm_wait_st();
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                double2 c0[4], c1[4];
+                if (ev == 0) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) c0[i] = c1[i] = make_double2(0.0, 0.0);
+                } else {
+                    double d[16], unused[8];
+                    tm_load16<0>(d, unused, tm_acc + 32 * h, 0);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { c0[i] = make_double2(d[2 * i], d[2 * i + 1]); c1[i] = make_double2(d[8 + 2 * i], d[9 + 2 * i]); }
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int r = 4 * h + i;
+                    const double2 b0 = rows.load(row + r * 64);
+                    const double2 b1 = rows.load(row + kM + r * 64);
+                    c0[i].x = fma(x[r].x, b0.x, c0[i].x);
+                    c0[i].x = fma(-x[r].y, b0.y, c0[i].x);
+                    c0[i].y = fma(x[r].x, b0.y, c0[i].y);
+                    c0[i].y = fma(x[r].y, b0.x, c0[i].y);
+                    c1[i].x = fma(x[r].x, b1.x, c1[i].x);
+                    c1[i].x = fma(-x[r].y, b1.y, c1[i].x);
+                    c1[i].y = fma(x[r].x, b1.y, c1[i].y);
+                    c1[i].y = fma(x[r].y, b1.x, c1[i].y);
+                }
+                tm_store16(tm_acc + 32 * h, c0[0].x, c0[0].y, c0[1].x, c0[1].y, c0[2].x, c0[2].y, c0[3].x, c0[3].y,
+                           c1[0].x, c1[0].y, c1[1].x, c1[1].y, c1[2].x, c1[2].y, c1[3].x, c1[3].y);
+            }
+            rows.release(ev);
+        }
+    }
+    tm_wait_st();
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+        double2 acc[8];
+        {
+            double d[16], unused[8];
+            // column c of both halves: 16 columns at +16 c of each half
+            asm volatile("{\n\t.reg .b32 u<16>, v<16>;\n\t" TM_LD_L16("u", "%16") TM_LD_L16("v", "%17")
+                         "tcgen05.wait::ld.sync.aligned;\n\t"
+                         TM_PACK8("%0", "%1", "%2", "%3", "%4", "%5", "%6", "%7", "u") TM_PACK8("%8", "%9", "%10", "%11", "%12", "%13", "%14", "%15", "v") "}"
+                         : "=d"(d[0]), "=d"(d[1]), "=d"(d[2]), "=d"(d[3]), "=d"(d[4]), "=d"(d[5]), "=d"(d[6]), "=d"(d[7]),
+                           "=d"(d[8]), "=d"(d[9]), "=d"(d[10]), "=d"(d[11]), "=d"(d[12]), "=d"(d[13]), "=d"(d[14]), "=d"(d[15])
+                         : "r"(tm_acc + 16 * c), "r"(tm_acc + 32 + 16 * c) : "memory");
+            (void)unused;
+#pragma unroll
+            for (int r = 0; r < 8; ++r) acc[r] = make_double2(d[2 * r], d[2 * r + 1]);
+        }
+        bar();   // exchange buffer free
+        fft.template inverse<true>(acc, buf, bar);
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const int j = c * kN + t + 64 * r;
+            const double sc = c_tw.p1_scale[r];   // 1/512 times the cos factors the last pass left out
+            const int32_t lo = round_scaled_to_torus(acc[r].x, sc), hi = round_scaled_to_torus(acc[r].y, sc);
+            if (MODE == 0) { ACC[j] += lo; ACC[j + kM] += hi; }
+            else           { ACC[j] = lo;  ACC[j + kM] = hi; }
+        }
+    }
+    bar();  // accumulator complete before the next step's rotated reads; exchange buffer free
+}
+template <int L, int BGBIT, int MODE, class Barrier, class Rows>
+__device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int a, const Rows &rows,
+                                          const FftTmS &fft, const Barrier &bar) {
+    cmux_step_single_tmacc<L, BGBIT, MODE>(ACC, bufs, a, rows, fft, bar);
+}
+
 // per ciphertext group: ACC + 2 exchange buffers + bara
-template <class FFT> __host__ __device__ constexpr int group_smem_bytes() { return 2 * kN * 4 + 2 * FFT::kBufElemsPerTransform * 16 + 1280; }
+template <class FFT> __host__ __device__ constexpr int group_smem_bytes() {
+    return 2 * kN * 4 + FFT::kExchangeBuffers * FFT::kBufElemsPerTransform * 16 + 1280;
+}
 constexpr int kGroupSmemBytes = 2 * kN * 4 + 2 * kBufElems * 16 + 1280;   // FftSmem (also the experiments' kernels)
 constexpr int kBrStages = 4;
 template <class FFT> __host__ __device__ constexpr int br_smem_bytes(int groups, int stages) {
@@ -611,12 +778,12 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
     unsigned char *mine = smem + STAGES * kStageBytes + 128 + (size_t)g * group_smem_bytes<FFT>();
     int32_t *ACC = reinterpret_cast<int32_t *>(mine);                                // [2][1024]
     double2 *bufs = reinterpret_cast<double2 *>(mine + 2 * kN * 4);                  // [2][576 | 512]
-    uint16_t *bara = reinterpret_cast<uint16_t *>(mine + 2 * kN * 4 + 2 * FFT::kBufElemsPerTransform * 16);  // [n+1]
+    uint16_t *bara = reinterpret_cast<uint16_t *>(mine + 2 * kN * 4 + FFT::kExchangeBuffers * FFT::kBufElemsPerTransform * 16);  // [n+1]
     const double2 *bkfft = UsesTm<FFT>::value ? key.bkfft_tm : key.bkfft;
     uint32_t *tm_slot_p = reinterpret_cast<uint32_t *>(smem + STAGES * kStageBytes + 120);   // behind the ring state
     uint32_t tm = 0;
-    static_assert(!UsesTm<FFT>::value || ((2 * G + 3) / 4) * TmWindow<FFT>::value <= 512, "tensor-memory columns of the warps sharing a lane quarter");
-    if (UsesTm<FFT>::value) tm = tm_alloc_cta(tm_slot_p, TmWindow<FFT>::value);
+    static_assert(!UsesTm<FFT>::value || TmShared<FFT>::value + ((2 * G + 3) / 4) * TmWindow<FFT>::value <= 512, "tensor-memory columns of the warps sharing a lane quarter");
+    if (UsesTm<FFT>::value) tm = tm_alloc_cta(tm_slot_p, TmWindow<FFT>::value, TmShared<FFT>::value);
 
     const int n = key.n, n1 = n + 1;
     const int bmin = min((int)blockIdx.x, a.bal_r);
@@ -671,17 +838,28 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
         }
     }
     FFT fft;
-    fft.init(t, tm);
+    if constexpr (TmShared<FFT>::value != 0) fft.init(t, tm, (tm & 0xffff0000u) | (*tm_slot_p & 0xffffu));   // roots: columns 0.. of the lane quarter
+    else fft.init(t, tm);
     const NamedBarrier64 bar{1 + g};
     bar();
+    if (a.stagger > 0) {
+        const long long until = clock64() + (long long)a.stagger * (g >> 1);
+        while (clock64() < until) {}
+    }
 
     // ---- blind rotation (lwe-bootstrapping-functions-fft.cpp:88-112)
-    RingRows<STAGES> rows{ring, st, bkfft, 0, total, 2 * G};
+    int lane_id = threadIdx.x & 31;
+    asm volatile("" : "+r"(lane_id));   // keep it in a register: the compiler otherwise re-reads SR_TID in the loop
+    RingRows<STAGES> rows{ring, st, bkfft, 0, total, 2 * G, lane_id == 0};
 #pragma unroll 1
     for (int i = 0; i < n; ++i) {
         rows.seq0 = i * KPL;
         const int ai = live ? bara[i] : 0;
-        if (ai == 0) { rows.skip_step(KPL); continue; }
+        if (ai == 0) {
+            if (PairEvents<FFT>::value) rows.skip_step_pairs(L);
+            else rows.skip_step(KPL);
+            continue;
+        }
         cmux_step<L, BGBIT, 0>(ACC, bufs, ai, rows, fft, bar);
     }
 
@@ -968,6 +1146,11 @@ static cudaError_t br_launch_st(const DeviceKey &key, const BlindRotateArgs &a, 
     }
     unsigned grid = (unsigned)((a.items + G - 1) / G);
     BlindRotateArgs b = a;
+    {
+        static int stagger = -1;
+        if (stagger < 0) { const char *ev = getenv("B200_STAGGER"); stagger = ev ? atoi(ev) : 0; }
+        b.stagger = stagger;
+    }
     if (G > 1 && br_balance()) {
         // whole waves of one CTA per SM, items spread evenly over them: the last wave then runs CTAs
         // with fewer ciphertexts (which finish sooner) on every SM instead of full CTAs on a few
@@ -1008,14 +1191,31 @@ bool experiments_built() {
     return false;
 #endif
 }
-static int br_variant() {
+// 0 "v2": shared-memory transforms; 1..8: round-1 experiments; 9 "tm", 10 "tmacc", 11 "tms": tensor-memory
+// transforms (round 2); 12 "auto" (default): tmacc where it is the fastest (l = 2, more than 4 ciphertexts per SM),
+// v2 and the latency kernel elsewhere
+constexpr int kVarAuto = 12;
+static int br_variant_raw() {
     int v = g_br_variant.load();
     if (v < 0) {
         const char *e = getenv("B200_BR_KERNEL");
-        v = (e && e[0] == 'w') ? 1 : (e && e[0] >= '0' && e[0] <= '9') ? atoi(e) : 0;
+        v = (e && e[0] == 'w') ? 1 : (e && e[0] >= '0' && e[0] <= '9') ? atoi(e) : kVarAuto;
         g_br_variant.store(v);
     }
     return v;
+}
+static bool br_tm_g_forced() {
+    static const bool forced = getenv("B200_TM_G") != nullptr;
+    return forced;
+}
+// the variant that decides everything but the wide l = 2 launch, and whether that launch is the tmacc kernel
+static int br_variant() {
+    const int v = br_variant_raw();
+    return (v == kVarAuto || (v == 10 && !br_tm_g_forced())) ? 0 : v;
+}
+static bool br_wide_tmacc() {
+    const int v = br_variant_raw();
+    return v == kVarAuto || (v == 10 && !br_tm_g_forced());
 }
 #ifdef B200_EXPERIMENTS
 template <int L, int BGBIT, int G>
@@ -1107,14 +1307,29 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         return cudaGetLastError();
     }
 #endif
+    if (br_variant() == 11 && a.items > 148 * 4 && key.l == 2 && key.Bgbit == 10) {
+        // "tms": single transforms, accumulators in tensor memory for every row, 6 / 7 / 8 groups per SM
+        static int tmg = -1;
+        if (tmg < 0) { const char *ev = getenv("B200_TM_G"); tmg = ev ? atoi(ev) : 8; }
+        cudaError_t et = tmg == 6 ? br_launch_st<2, 10, 6, 7, FftTmS>(key, a, s)
+                       : tmg == 7 ? br_launch_st<2, 10, 7, 6, FftTmS>(key, a, s)
+                                  : br_launch_st<2, 10, 8, 5, FftTmS>(key, a, s);
+        if (et != cudaSuccess) return et;
+        COUNT_LAUNCH();
+        return cudaGetLastError();
+    }
     if (br_variant() == 10 && a.items > 148 * 4) {
         // "tmacc": the tm kernel with the spectral accumulators parked in tensor memory between row pairs
         cudaError_t et;
         static int tmg = -1;
         if (tmg < 0) { const char *ev = getenv("B200_TM_G"); tmg = ev ? atoi(ev) : 6; }
         if (key.l == 2 && key.Bgbit == 10 && tmg == 4) et = br_launch_tm<2, 10, 4, FftTmAcc>(key, a, s);
+        else if (key.l == 2 && key.Bgbit == 10 && tmg == 5) et = br_launch_tm<2, 10, 5, FftTmAcc>(key, a, s);
         else if (key.l == 2 && key.Bgbit == 10) et = br_launch_tm<2, 10, 6, FftTmAcc>(key, a, s);
+        else if (key.l == 3 && key.Bgbit == 7 && tmg == 4) et = br_launch_tm<3, 7, 4, FftTmAcc>(key, a, s);
+        else if (key.l == 3 && key.Bgbit == 7 && tmg == 5) et = br_launch_tm<3, 7, 5, FftTmAcc>(key, a, s);
         else if (key.l == 3 && key.Bgbit == 7) et = br_launch_tm<3, 7, 6, FftTmAcc>(key, a, s);
+        else if (key.l == 2 && key.Bgbit == 8) et = br_launch_tm<2, 8, 6, FftTmAcc>(key, a, s);
         else return cudaErrorInvalidValue;
         if (et != cudaSuccess) return et;
         COUNT_LAUNCH();
@@ -1165,12 +1380,12 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
                 if (r.in1) r.in1 += rows;
                 if (r.in2) r.in2 += rows;
             }
-            e = br_launch<2, 10, 6>(key, h, s);
+            e = br_wide_tmacc() ? br_launch_tm<2, 10, 6, FftTmAcc>(key, h, s) : br_launch<2, 10, 6>(key, h, s);
             if (e != cudaSuccess) return e;
             COUNT_LAUNCH();
             return launch_blind_rotate(key, r, s);
         }
-        e = br_launch<2, 10, 6>(key, a, s);
+        e = br_wide_tmacc() ? br_launch_tm<2, 10, 6, FftTmAcc>(key, a, s) : br_launch<2, 10, 6>(key, a, s);
     } else
     if (key.l == 2 && key.Bgbit == 10) BR_LAUNCH(2, 10);
     else if (key.l == 3 && key.Bgbit == 7) BR_LAUNCH(3, 7);
@@ -1206,7 +1421,7 @@ cudaError_t launch_cmux_test(const DeviceKey &key, int32_t *d_acc, int bk_index,
         return cudaGetLastError();
     }
 #endif
-    if (br_variant() == 9 || br_variant() == 10) {
+    if ((br_variant_raw() >= 9 && br_variant_raw() <= 11) || (br_variant_raw() == kVarAuto && key.l == 2 && key.Bgbit == 10)) {
         int dev = 0;
         cudaGetDevice(&dev);
         const unsigned grid = (unsigned)std::min<int64_t>(count, sm_count_of(dev));

@@ -31,7 +31,8 @@ namespace b200 {
 
 constexpr int kTmBufElems = 512;          // one exchange buffer: 8 KiB, no padding
 constexpr int kTmColsPerWarp = 128;       // 0-31, 32-63 exchange windows A, B | 64-79 P2 roots | 80-91 P3a roots | 96-103 P3b roots
-constexpr int kTmColExB = 32, kTmColRoots2 = 64, kTmColRoots3a = 80, kTmColRoots3b = 96;
+constexpr int kTmColExB = 32, kTmColRootsBase = 64;
+constexpr int kTmColRoots2 = 0, kTmColRoots3a = 16, kTmColRoots3b = 32;   // relative to the roots base (FftTm::tmr)
 
 struct TmRootTables {
     double2 p3a[32][3];                   // A = s(6, 2b'), C = s(7, 4b'), D = s(7, 4b'+2);  b' = e >> 4
@@ -249,8 +250,10 @@ __device__ __forceinline__ void inv_p3b(double2 (&x)[8], const double2 E0, const
 // warp's lane quarter, column field = window base).
 struct FftTm {
     static constexpr int kBufElemsPerTransform = kTmBufElems;
+    static constexpr int kExchangeBuffers = 2;
     int t;
-    uint32_t tm;
+    uint32_t tm;   // exchange window(s) of this warp
+    uint32_t tmr;  // roots of this thread: 40 columns of its lane (per warp, or shared by the warps of a lane quarter)
     int rd0;       // element index of register 0 in the P2 layout (registers add 8 r): shared-memory read base
 
     __device__ __forceinline__ static int elem_p2(int t) {
@@ -258,19 +261,21 @@ struct FftTm {
         return ((t >> 5) << 8) | ((lane & 3) << 6) | (((lane >> 4) & 1) << 2) | (((lane >> 3) & 1) << 1) | ((lane >> 2) & 1);
     }
     // one-time: this thread's roots into its tensor-memory lane
-    __device__ __forceinline__ void init(int t_, uint32_t tm_) {
+    __device__ __forceinline__ void init(int t_, uint32_t tm_) { init(t_, tm_, tm_ + kTmColRootsBase); }
+    __device__ __forceinline__ void init(int t_, uint32_t tm_, uint32_t tmr_) {
         t = t_;
         tm = tm_;
+        tmr = tmr_;
         rd0 = elem_p2(t);
         const int lane = t & 31, w = t >> 5;
         const RootSet &p2 = c_tw.p2[4 * w + (lane & 3)];
-        tm_store4(tm + kTmColRoots2, p2.A.x, p2.A.y, p2.B.x, p2.B.y);
-        tm_store4(tm + kTmColRoots2 + 8, p2.C.x, p2.C.y, p2.D.x, p2.D.y);
+        tm_store4(tmr + kTmColRoots2, p2.A.x, p2.A.y, p2.B.x, p2.B.y);
+        tm_store4(tmr + kTmColRoots2 + 8, p2.C.x, p2.C.y, p2.D.x, p2.D.y);
         const double2 *a = c_tw_tm.p3a[16 * w + (lane & 15)];
-        tm_store4(tm + kTmColRoots3a, a[0].x, a[0].y, a[1].x, a[1].y);
-        tm_store4(tm + kTmColRoots3a + 8, a[2].x, a[2].y, 0.0, 0.0);
+        tm_store4(tmr + kTmColRoots3a, a[0].x, a[0].y, a[1].x, a[1].y);
+        tm_store4(tmr + kTmColRoots3a + 8, a[2].x, a[2].y, 0.0, 0.0);
         const double2 *b = c_tw_tm.p3b[t];
-        tm_store4(tm + kTmColRoots3b, b[0].x, b[0].y, b[1].x, b[1].y);
+        tm_store4(tmr + kTmColRoots3b, b[0].x, b[0].y, b[1].x, b[1].y);
         tm_wait_st();
     }
 
@@ -281,7 +286,7 @@ struct FftTm {
 #pragma unroll
         for (int r = 0; r < 8; ++r) buf[tm_slot(t + 64 * r)] = x[r];
         double rt[8];
-        tm_load_roots8(rt, tm + kTmColRoots2);     // x is dead here: the roots cost no registers before the barrier
+        tm_load_roots8(rt, tmr + kTmColRoots2);     // x is dead here: the roots cost no registers before the barrier
         bar();
         const int base = tm_slot(rd0);             // + 8 r: the swizzle depends on element bits 7,6 only
 #pragma unroll
@@ -295,12 +300,12 @@ struct FftTm {
         Tm8 lo, hi;
         tm_exchange_fwd_store<1>(x, tm);
         tm_wait_st();
-        tm_exchange_fwd_load<6>(lo, hi, rt, tm, tm + (16u << 16), tm + kTmColRoots3a);
+        tm_exchange_fwd_load<6>(lo, hi, rt, tm, tm + (16u << 16), tmr + kTmColRoots3a);
         tm_unpack(x, lo, hi);
         fwd_p3a(x, make_double2(rt[0], rt[1]), make_double2(rt[2], rt[3]), make_double2(rt[4], rt[5]));
         tm_exchange_fwd_store<2>(x, tm);
         tm_wait_st();
-        tm_exchange_fwd_load<4>(lo, hi, rt, tm, tm + (16u << 16), tm + kTmColRoots3b);
+        tm_exchange_fwd_load<4>(lo, hi, rt, tm, tm + (16u << 16), tmr + kTmColRoots3b);
         tm_unpack(x, lo, hi);
         fwd_p3b(x, make_double2(rt[0], rt[1]), make_double2(rt[2], rt[3]));
     }
@@ -310,9 +315,11 @@ struct FftTm {
     // profiles/r2_microbench_tmem.txt) is hidden inside the warp instead of by other warps, and every butterfly
     // level has twice the independent DFMA chains.  bufa / bufb: two exchange buffers; the caller guarantees that
     // nobody still reads them (group barrier after the previous transform's reads).
-    template <class Barrier>
+    struct NoMid { __device__ __forceinline__ void operator()() const {} };
+    // mid(): called when xa is complete and xb's last exchange is in flight (the caller's spectral MAC of xa)
+    template <class Barrier, class Mid = NoMid>
     __device__ __forceinline__ void forward2(double2 (&xa)[8], double2 (&xb)[8], double2 *bufa, double2 *bufb,
-                                             const Barrier &bar) const {
+                                             const Barrier &bar, const Mid &mid = Mid()) const {
         const uint32_t tma = tm, tmb = tm + kTmColExB;
         fwd_radix8(xa, c_tw.p1);
 #pragma unroll
@@ -321,7 +328,7 @@ struct FftTm {
 #pragma unroll
         for (int r = 0; r < 8; ++r) bufb[tm_slot(t + 64 * r)] = xb[r];
         double rt[8], r3[8];
-        tm_load_roots8(rt, tm + kTmColRoots2);
+        tm_load_roots8(rt, tmr + kTmColRoots2);
         bar();
         const int base = tm_slot(rd0);
 #pragma unroll
@@ -336,7 +343,7 @@ struct FftTm {
         tm_exchange_fwd_store<1>(xa, tma);
         fwd_radix8(xb, w2);                     // hides a's store
         tm_wait_st();
-        tm_exchange_fwd_load<6>(lo, hi, r3, tma, tma + (16u << 16), tm + kTmColRoots3a);
+        tm_exchange_fwd_load<6>(lo, hi, r3, tma, tma + (16u << 16), tmr + kTmColRoots3a);
         tm_exchange_fwd_store<1>(xb, tmb);
         tm_unpack(xa, lo, hi);
         const double2 A = make_double2(r3[0], r3[1]), C = make_double2(r3[2], r3[3]), D = make_double2(r3[4], r3[5]);
@@ -347,13 +354,14 @@ struct FftTm {
         tm_unpack(xb, lo, hi);
         fwd_p3a(xb, A, C, D);
         tm_wait_st();
-        tm_exchange_fwd_load<4>(lo, hi, r3, tma, tma + (16u << 16), tm + kTmColRoots3b);
+        tm_exchange_fwd_load<4>(lo, hi, r3, tma, tma + (16u << 16), tmr + kTmColRoots3b);
         tm_exchange_fwd_store<2>(xb, tmb);
         tm_unpack(xa, lo, hi);
         const double2 E0 = make_double2(r3[0], r3[1]), E1 = make_double2(r3[2], r3[3]);
         fwd_p3b(xa, E0, E1);
         tm_wait_st();
         tm_exchange_fwd_load<0>(lo, hi, rt, tmb, tmb + (16u << 16), 0);
+        mid();
         tm_unpack(xb, lo, hi);
         fwd_p3b(xb, E0, E1);
     }
@@ -363,7 +371,7 @@ struct FftTm {
                                              const Barrier &bar) const {
         const uint32_t tma = tm, tmb = tm + kTmColExB;
         double rt[8], r3[8], d[16];
-        tm_load_roots8(r3, tm + kTmColRoots3b);
+        tm_load_roots8(r3, tmr + kTmColRoots3b);
         {
             const double2 E0 = make_double2(r3[0], r3[1]), E1 = make_double2(r3[2], r3[3]);
             inv_p3b(xa, E0, E1);
@@ -371,7 +379,7 @@ struct FftTm {
             inv_p3b(xb, E0, E1);
         }
         tm_wait_st();
-        tm_load16<6>(d, r3, tma, tm + kTmColRoots3a);
+        tm_load16<6>(d, r3, tma, tmr + kTmColRoots3a);
         tm_exchange_inv_store(xb, tmb);
         tm_unpack_inv<2>(xa, d);
         const double2 A = make_double2(r3[0], r3[1]), C = make_double2(r3[2], r3[3]), D = make_double2(r3[4], r3[5]);
@@ -382,7 +390,7 @@ struct FftTm {
         tm_unpack_inv<2>(xb, d);
         inv_p3a(xb, A, C, D);
         tm_wait_st();
-        tm_load16<8>(d, rt, tma, tm + kTmColRoots2);
+        tm_load16<8>(d, rt, tma, tmr + kTmColRoots2);
         tm_exchange_inv_store(xb, tmb);
         tm_unpack_inv<1>(xa, d);
         RootSet w2;
@@ -411,16 +419,16 @@ struct FftTm {
     template <bool DEFER_LAST, class Barrier>
     __device__ __forceinline__ void inverse(double2 (&x)[8], double2 *buf, const Barrier &bar) const {
         double rt[8], d[16];
-        tm_load_roots8(rt, tm + kTmColRoots3b);    // (E0, E1 and 8 unused columns)
+        tm_load_roots8(rt, tmr + kTmColRoots3b);    // (E0, E1 and 8 unused columns)
         inv_p3b(x, make_double2(rt[0], rt[1]), make_double2(rt[2], rt[3]));
         tm_exchange_inv_store(x, tm);
         tm_wait_st();
-        tm_load16<6>(d, rt, tm, tm + kTmColRoots3a);
+        tm_load16<6>(d, rt, tm, tmr + kTmColRoots3a);
         tm_unpack_inv<2>(x, d);
         inv_p3a(x, make_double2(rt[0], rt[1]), make_double2(rt[2], rt[3]), make_double2(rt[4], rt[5]));
         tm_exchange_inv_store(x, tm);
         tm_wait_st();
-        tm_load16<8>(d, rt, tm, tm + kTmColRoots2);
+        tm_load16<8>(d, rt, tm, tmr + kTmColRoots2);
         tm_unpack_inv<1>(x, d);
         {
             RootSet w2;
@@ -444,10 +452,19 @@ struct FftTm {
 constexpr int kTmColAcc = 104;            // 104-167: acc0, acc1 (32 doubles)
 constexpr int kTmColsPerWarpAcc = 168;
 struct FftTmAcc : FftTm {};
+// Single transforms, accumulators in tensor memory for EVERY key row, one exchange buffer: what fits eight groups
+// (16 warps, 128 registers per thread) on an SM.  Tensor-memory columns of a lane quarter: 0-39 the roots, shared
+// by the four warps of the quarter (they hold the same half of the 64 threads); then per warp 32 exchange + 64
+// accumulator columns.
+constexpr int kTmSColsRoots = 64, kTmSColsPerWarp = 96, kTmSColAcc = 32;
+struct FftTmS : FftTm {
+    static constexpr int kExchangeBuffers = 1;
+};
 
 // the shared-memory transform of negacyclic_fft.cuh behind the same interface
 struct FftSmem {
     static constexpr int kBufElemsPerTransform = kBufElems;
+    static constexpr int kExchangeBuffers = 2;
     int t;
     RootSet w2, w3;
     __device__ __forceinline__ void init(int t_, uint32_t) {

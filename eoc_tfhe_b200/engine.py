@@ -287,8 +287,11 @@ def fp64_peak_tflops(device=0):
 
 
 def set_blind_rotate_kernel(variant):
-    """0 / "v2": 64 threads per ciphertext (default); 1 / "w16": warp per ciphertext with TMEM accumulators."""
-    v = {"v2": 0, "w16": 1, "v3g6": 2, "v3c2": 3, "v3g5": 4, "v3g4": 5, "v3g3c2": 6, "v4": 7, "v5": 8, "tm": 9, "tmacc": 10}.get(variant, variant)
+    """12 / "auto" (default): the fastest kernel per launch ("tmacc" for wide batches at l = 2, else "v2" and the
+    latency kernel); 0 / "v2": shared-memory transforms; 9 / "tm", 10 / "tmacc", 11 / "tms": tensor-memory transforms
+    (exchanges and roots in tensor memory; + accumulators; single transforms); 1..8: round-1 experiments (only in a
+    B200_EXPERIMENTS build)."""
+    v = {"v2": 0, "w16": 1, "v3g6": 2, "v3c2": 3, "v3g5": 4, "v3g4": 5, "v3g3c2": 6, "v4": 7, "v5": 8, "tm": 9, "tmacc": 10, "tms": 11, "auto": 12}.get(variant, variant)
     _lib.check(_lib.load().b200_set_blind_rotate_kernel(int(v)))
 
 

@@ -1,4 +1,5 @@
 """A/B: blind-rotation kernels v2 / tm on N rotations (timing from the library's CUDA events)."""
+import os
 import sys
 import numpy as np, torch
 sys.path.insert(0, ".")
@@ -15,7 +16,8 @@ for count in counts:
     a = torch.randint(-2**31, 2**31 - 1, (count, P.n + 1), dtype=torch.int32, device="cuda", generator=g)
     b = torch.randint(-2**31, 2**31 - 1, (count, P.n + 1), dtype=torch.int32, device="cuda", generator=g)
     outs = {}
-    for v in ("v2", "tm", "tmacc"):
+    variants = os.environ.get("AB_VARIANTS", "v2,tm,tmacc").split(",")
+    for v in variants:
         set_blind_rotate_kernel(v)
         out = torch.empty_like(a)
         for _ in range(2): ck.gate(GateOp.NAND, a, b, out=out)
@@ -25,4 +27,4 @@ for count in counts:
         tm = ck.timing_drain()
         outs[v] = out.clone()
         print("P%d %s %d items: blind_rotate %.3f ms, keyswitch %.3f ms" % (lam, v, count, tm["blind_rotate"] / tm["calls"], tm["keyswitch"] / tm["calls"]), flush=True)
-    print("   tm == v2:", bool(torch.equal(outs["v2"], outs["tm"])), " tmacc == v2:", bool(torch.equal(outs["v2"], outs["tmacc"])), flush=True)
+    print("   equal to %s:" % variants[0], {v: bool(torch.equal(outs[variants[0]], outs[v])) for v in variants[1:]}, flush=True)

@@ -22,8 +22,9 @@ __global__ void __launch_bounds__(THREADS, 1) k(int mode, double *sink, long lon
 #pragma unroll
     for (int r = 0; r < 8; ++r) { x[r] = t - r; a[r] = 1.0 - 1e-9 * (t + r) * seed; b[r] = 1e-9 * (r + 1) * seed; }
     double2 z[8];
+    int iv[8];
 #pragma unroll
-    for (int r = 0; r < 8; ++r) z[r] = make_double2(t + r, t - r);
+    for (int r = 0; r < 8; ++r) { z[r] = make_double2(t + r, t - r); iv[r] = t * 977 + r; }
     double2 w0 = make_double2(0.7 * seed, 0.3 * seed), w1 = make_double2(0.6 * seed, 0.2 * seed), w2 = make_double2(0.5 * seed, 0.1 * seed);
     const double c = 1.0 - 1e-9 * seed, e = 1e-9 * seed;
     __syncthreads();
@@ -52,17 +53,39 @@ __global__ void __launch_bounds__(THREADS, 1) k(int mode, double *sink, long lon
             bf(z[0], z[1], w2); bf(z[2], z[3], w2); bf(z[4], z[5], w2); bf(z[6], z[7], w2);
 #pragma unroll
             for (int r = 0; r < 8; ++r) { z[r].x *= 0.25; z[r].y *= 0.25; }   // keep values bounded (16 DMUL extra)
-        } else {
+        } else if (mode == 4) {
 #pragma unroll
             for (int k2 = 0; k2 < 9; ++k2)
 #pragma unroll
                 for (int r = 0; r < 8; ++r) x[r] = fma(a[(r + k2) & 7], c_k[k2 & 7], x[r]);
+        } else {
+            // mode 5: 72 DFMA (as mode 0) + 16 I2F.F64.S32; mode 6: the 16 I2F alone; mode 7: 72 DFMA + 16 DADD conversions
+            if (mode != 6) {
+#pragma unroll
+                for (int k2 = 0; k2 < 9; ++k2)
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) x[r] = fma(x[r], c, e);
+            }
+            if (mode == 5 || mode == 6) {
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    iv[r] = iv[r] * 3 + it;
+                    b[r] += (double)(iv[r] >> 20) + (double)((iv[r] << 10) >> 22);
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    iv[r] = iv[r] * 3 + it;
+                    b[r] += (__hiloint2double(0x43300000, (iv[r] >> 20) & 1023) - 4503599627370496.0) +
+                            (__hiloint2double(0x43300000, (iv[r] >> 10) & 1023) - 4503599627370496.0);
+                }
+            }
         }
     }
     const long long t1 = clock64();
     double s = 0;
 #pragma unroll
-    for (int r = 0; r < 8; ++r) s += x[r] + a[r] + b[r] + z[r].x + z[r].y;
+    for (int r = 0; r < 8; ++r) s += x[r] + a[r] + b[r] + z[r].x + z[r].y + iv[r];
     if (s == 123.456) sink[0] = s;
     if (t == 0) cycles[blockIdx.x] = t1 - t0;
 }
@@ -88,7 +111,9 @@ int main() {
 #define ALL(T) \
     run<T>(0, "72 DFMA x = fma(x, c, e)", 72, sink, cyc); run<T>(1, "72 DFMA x = fma(a_r, b_r, x), 3 distinct operands", 72, sink, cyc); \
     run<T>(2, "72 DFMA x = fma(a_r, c, x)", 72, sink, cyc); run<T>(3, "radix-8 pass: 72 DFMA + 16 DMUL", 88, sink, cyc); \
-    run<T>(4, "72 DFMA x = fma(a_r, c[bank], x)", 72, sink, cyc);
+    run<T>(4, "72 DFMA x = fma(a_r, c[bank], x)", 72, sink, cyc); \
+    run<T>(6, "16 I2F.F64.S32 + 16 DADD alone", 32, sink, cyc); run<T>(5, "72 DFMA + 16 I2F.F64.S32 + 16 DADD", 88, sink, cyc); \
+    run<T>(7, "72 DFMA + 16 magic-number conversions + 24 DADD", 112, sink, cyc);
     ALL(128) ALL(256) ALL(384)
     printf("status: %s\n", cudaGetErrorString(cudaGetLastError()));
     return 0;

@@ -28,7 +28,7 @@ def keys(request):
     ck = CloudKey.from_libtfhe(rk.cloud_ptr)
     yield rk, ck
     ck.close()
-    set_blind_rotate_kernel("v2")
+    set_blind_rotate_kernel("auto")
 
 
 def test_params_roundtrip(keys):

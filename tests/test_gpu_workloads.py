@@ -31,7 +31,7 @@ TRUTH = {
 @pytest.fixture(scope="module")
 def p80():
     from eoc_tfhe_b200 import CloudKey, set_blind_rotate_kernel
-    set_blind_rotate_kernel("v2")
+    set_blind_rotate_kernel("auto")
     ref = reflib.RefLib()
     rk = ref.keygen(80, seed=1234)
     ck = CloudKey.from_libtfhe(rk.cloud_ptr)
@@ -286,7 +286,7 @@ def test_tm_blind_rotation_bit_identical(p80):
         out = ck.gate(GateOp.NAND, np.tile(cts, (15, 1)), np.tile(cts, (15, 1)))
         assert np.array_equal(rk.decrypt_bits(out), np.tile(1 - bits, 15))
     finally:
-        set_blind_rotate_kernel("v2")
+        set_blind_rotate_kernel("auto")
 
 
 def test_tensor_memory_blind_rotation_variants_bit_identical(p80):
@@ -318,7 +318,7 @@ def test_tensor_memory_blind_rotation_variants_bit_identical(p80):
         assert np.array_equal(ck.bootstrap_woks(x[:1]), want[:1])
         assert np.array_equal(ck.bootstrap_woks(x[:300]), want[:300])
     finally:
-        set_blind_rotate_kernel("v2")
+        set_blind_rotate_kernel("auto")
     # and the result is the reference's up to FFT rounding: same decrypted bit after key switch on real ciphertexts
     bits = rng.integers(0, 2, size=64).astype(np.int32)
     cts = rk.encrypt_bits(bits)
@@ -329,7 +329,7 @@ def test_tensor_memory_blind_rotation_variants_bit_identical(p80):
         a = torch.from_numpy(np.tile(cts, (10, 1))).cuda()
         out = ck.gate(GateOp.NAND, a, a)
     finally:
-        set_blind_rotate_kernel("v2")
+        set_blind_rotate_kernel("auto")
     assert np.array_equal(rk.decrypt_bits(out.cpu().numpy()), np.tile(1 - bits, 10))
 
 
