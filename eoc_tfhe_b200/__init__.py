@@ -8,6 +8,6 @@ implementation -- `lib.load()` raises if the library is missing.
 """
 from .lib import load, LIB_PATH, B200Error  # noqa: F401
 from .engine import (  # noqa: F401
-    GateOp, Params, CloudKey, PARAMS_80, PARAMS_128, launch_count, fp64_peak_tflops, set_blind_rotate_kernel, set_keyswitch_kernel, experiments_built,
+    GateOp, Params, CloudKey, PARAMS_80, PARAMS_128, launch_count, fp64_peak_tflops, int32_add_peak, set_blind_rotate_kernel, set_keyswitch_kernel, experiments_built, fft_roundtrip, poly_mul,
 )
 from . import circuits, eoc, shard, wire  # noqa: F401

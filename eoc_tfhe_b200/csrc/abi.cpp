@@ -17,6 +17,7 @@
 #include <new>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 using namespace b200;
@@ -92,19 +93,21 @@ static int check_params(const b200_params *p) {
     return 0;
 }
 
-static int key_alloc(const b200_params *p, b200_key **out) {
+static int key_alloc(const b200_params *p, b200_key **out, int device = -1) {
     if (!out) return fail("out is NULL");
     *out = nullptr;
     if (check_params(p)) return 1;
     if (b200_device_count() <= 0) return fail("no CUDA device: libb200tfhe has no CPU fallback");
-    B200_ON_DEVICE(g_device);
+    if (device < 0) device = g_device;
+    if (device >= b200_device_count()) return fail("device index out of range");
+    B200_ON_DEVICE(device);
     b200_key *k = new (std::nothrow) b200_key();
     if (!k) return fail("out of host memory");
     DeviceKey &d = k->dk;
     d.n = p->n; d.N = p->N; d.k = p->k; d.l = p->l; d.Bgbit = p->Bgbit;
     d.ks_t = p->ks_t; d.ks_basebit = p->ks_basebit; d.ks_variance = p->ks_variance;
     d.ks_stride = (p->n + 1 + 3) & ~3;
-    d.device = g_device;
+    d.device = device;
     const int kpl = (d.k + 1) * d.l, base = 1 << d.ks_basebit;
     // the evaluation-domain key is one blob (one broadcast replicates it); an experiments build appends the
     // layout of the warp-per-ciphertext transform
@@ -171,8 +174,21 @@ extern "C" int b200_key_create(const b200_params *p, const int32_t *bk_coefs, co
     return 0;
 }
 
+struct b200_multi;
+extern "C" void b200_multi_free(b200_multi *m);
+static std::map<b200_key *, b200_multi *> &multi_cache();
 extern "C" void b200_key_free(b200_key *k) {
     if (!k) return;
+    {
+        b200_multi *m = nullptr;
+        {
+            std::lock_guard<std::mutex> g(g_cache_mu);
+            auto &mc = multi_cache();
+            auto it = mc.find(k);
+            if (it != mc.end()) { m = it->second; mc.erase(it); }
+        }
+        if (m) b200_multi_free(m);
+    }
     {
         std::lock_guard<std::mutex> g(g_cache_mu);
         for (auto *m : {&g_by_cloud, &g_by_bkfft, &g_by_ks})
@@ -570,7 +586,186 @@ extern "C" int b200_fp64_peak_tflops(int device, double *tflops) {
     return 0;
 }
 
+// ---- several devices behind one handle -------------------------------------------------------------
+// The path shards by independent gates (no data-path collective): a b200_multi holds one replica of the cloud key
+// per device; a host batch is cut into contiguous slices, one per device, each evaluated by its own host thread
+// through the single-device entry (its own streams, workspaces and mutex).  The reference has no counterpart
+// (zero collectives); this is the C-ABI form of north_star's multi-GPU split.
+struct b200_multi {
+    std::vector<b200_key *> keys;     // keys[0] is the caller's key (not owned), the others are replicas (owned)
+};
+
+extern "C" int b200_multi_create(b200_key *key, const int32_t *devices, int32_t ndev, b200_multi **out) {
+    return b200_guarded([&]() -> int {
+        if (!key || !key->filled) return fail("key is NULL or not filled");
+        if (!out) return fail("out is NULL");
+        *out = nullptr;
+        const int have = b200_device_count();
+        std::vector<int> devs;
+        if (!devices) {                       // all devices, the key's own first
+            devs.push_back(key->dk.device);
+            for (int d = 0; d < have && (ndev <= 0 || (int)devs.size() < ndev); ++d)
+                if (d != key->dk.device) devs.push_back(d);
+        } else {
+            if (ndev < 1) return fail("ndev must be >= 1");
+            for (int i = 0; i < ndev; ++i) {
+                if (devices[i] < 0 || devices[i] >= have) return fail("device index out of range");
+                for (int d : devs) if (d == devices[i]) return fail("device listed twice");
+                devs.push_back(devices[i]);
+            }
+            if (devs[0] != key->dk.device) return fail("devices[0] must be the device the key lives on");
+        }
+        b200_multi *m = new b200_multi();
+        m->keys.push_back(key);
+        b200_params p;
+        b200_key_params(key, &p);
+        for (size_t i = 1; i < devs.size(); ++i) {
+            b200_key *r = nullptr;
+            int rc = key_alloc(&p, &r, devs[i]);
+            if (!rc) {
+                // replicate the two resident blobs device to device (NVLink when peers, through the host otherwise)
+                cudaError_t e = cudaMemcpyPeer(r->dk.bkfft, devs[i], key->dk.bkfft, key->dk.device, key->dk.bkfft_bytes);
+                if (e == cudaSuccess) e = cudaMemcpyPeer(r->dk.ks, devs[i], key->dk.ks, key->dk.device, key->dk.ks_bytes);
+                if (e != cudaSuccess) rc = fail_cuda("key replication", e);
+                else r->filled = true;
+            }
+            if (rc) {
+                if (r) b200_key_free(r);
+                for (size_t j = 1; j < m->keys.size(); ++j) b200_key_free(m->keys[j]);
+                delete m;
+                return 1;
+            }
+            m->keys.push_back(r);
+        }
+        *out = m;
+        return 0;
+    });
+}
+extern "C" void b200_multi_free(b200_multi *m) {
+    if (!m) return;
+    for (size_t j = 1; j < m->keys.size(); ++j) b200_key_free(m->keys[j]);
+    delete m;
+}
+extern "C" int b200_multi_device_count(const b200_multi *m) { return m ? (int)m->keys.size() : 0; }
+
+static int gate_batch_host_locked(b200_key *k, int op, int32_t *out, const int32_t *a, const int32_t *b, const int32_t *c,
+                                  int64_t count, int32_t *nonzero);
+static bool op_is_linear(int op);
+// slices of whole blind-rotation waves (148 SMs x 6), the remainder on the last device
+static int multi_gate_batch(b200_multi *m, int op, int32_t *out, const int32_t *a, const int32_t *b, const int32_t *c,
+                            int64_t count, int32_t *nonzero) {
+    const int nd = (int)m->keys.size();
+    const int n1 = m->keys[0]->dk.n + 1;
+    const int64_t quantum = 148 * 6;
+    int64_t per = (count + nd - 1) / nd;
+    per = (per + quantum - 1) / quantum * quantum;
+    if (nd == 1 || count <= quantum) {
+        std::lock_guard<std::mutex> g(m->keys[0]->mu);
+        return gate_batch_host_locked(m->keys[0], op, out, a, b, c, count, nonzero);
+    }
+    std::vector<int> rcs(nd, 0);
+    std::vector<std::string> errs(nd);
+    std::vector<std::thread> th;
+    for (int d = 0; d < nd; ++d) {
+        const int64_t g0 = std::min<int64_t>(count, d * per), g = std::min<int64_t>(per, count - g0);
+        if (g <= 0) break;
+        th.emplace_back([&, d, g0, g]() {
+            const size_t off = (size_t)g0 * n1;
+            b200_key *k = m->keys[d];
+            std::lock_guard<std::mutex> lk(k->mu);
+            rcs[d] = gate_batch_host_locked(k, op, out + off, a ? a + off : nullptr, b ? b + off : nullptr, c ? c + off : nullptr,
+                                            g, nonzero ? nonzero + g0 : nullptr);
+            if (rcs[d]) errs[d] = b200_last_error();    // the error message is thread local: carry it to the caller
+        });
+    }
+    for (auto &t : th) t.join();
+    for (int d = 0; d < nd; ++d)
+        if (rcs[d]) return fail("device " + std::to_string(m->keys[d]->dk.device) + ": " + errs[d]);
+    return 0;
+}
+extern "C" int b200_multi_gate_batch_host(b200_multi *m, int op, int32_t *out, const int32_t *a, const int32_t *b,
+                                          const int32_t *c, int64_t count) {
+    return b200_guarded([&]() -> int {
+        if (!m || m->keys.empty()) return fail("multi-device handle is NULL");
+        if (op < 0 || op >= B200_GATE_OP_COUNT) return fail("invalid gate op");
+        if (count < 0) return fail("negative count");
+        if (count == 0) return 0;
+        if (!out) return fail("out is NULL");
+        const char *o0 = (const char *)out;
+        const size_t bytes = (size_t)count * (m->keys[0]->dk.n + 1) * sizeof(int32_t);
+        for (const int32_t *in : {a, b, c}) {   // slices run concurrently: an output slice must not be another slice's input
+            const char *i0 = (const char *)in;
+            if (in && in != out && i0 < o0 + bytes && o0 < i0 + bytes) return fail("out overlaps an input at a different offset");
+        }
+        return multi_gate_batch(m, op, out, a, b, c, count, nullptr);
+    });
+}
+
+extern "C" int b200_int32_add_peak(int device, double *tera_adds_per_s) {
+    if (!tera_adds_per_s) return fail("NULL argument");
+    if (b200_device_count() <= 0) return fail("no CUDA device");
+    B200_ON_DEVICE(device);
+    CK(measure_int_add_peak(tera_adds_per_s));
+    return 0;
+}
+
 // ---- batched gate over libtfhe samples -----------------------------------------------------------
+// B200TFHE_DEVICES = "all" | N: the drop-in batched gate (bootsGate_batch) spreads batches of at least two waves
+// over that many devices; the replicas are made on first use and die with the key.
+static std::map<b200_key *, b200_multi *> g_multi;
+static std::map<b200_key *, b200_multi *> &multi_cache() { return g_multi; }
+static b200_multi *multi_for_key(b200_key *k) {
+    static const int want = [] {
+        const char *e = getenv("B200TFHE_DEVICES");
+        if (!e || !*e) return 1;
+        if (!std::strcmp(e, "all")) return b200_device_count();
+        return std::max(1, std::min(atoi(e), b200_device_count()));
+    }();
+    if (want <= 1) return nullptr;
+    {
+        std::lock_guard<std::mutex> g(g_cache_mu);
+        auto it = g_multi.find(k);
+        if (it != g_multi.end()) return it->second;
+    }
+    // (the caller holds k->mu, so nobody else creates replicas of this key now; the cache lock is not held while
+    // the replicas are made because a failing replica is freed through b200_key_free, which takes it)
+    b200_multi *m = nullptr;
+    if (b200_multi_create(k, nullptr, want, &m)) m = nullptr;   // fall back to one device, the error stays readable
+    std::lock_guard<std::mutex> g(g_cache_mu);
+    g_multi[k] = m;
+    return m;
+}
+// multi_gate_batch for a caller that already holds keys[0]->mu
+static int multi_gate_batch_locked0(b200_multi *m, int op, int32_t *out, const int32_t *a, const int32_t *b, const int32_t *c,
+                                    int64_t count, int32_t *nonzero) {
+    const int nd = (int)m->keys.size();
+    const int n1 = m->keys[0]->dk.n + 1;
+    const int64_t quantum = 148 * 6;
+    int64_t per = (count + nd - 1) / nd;
+    per = (per + quantum - 1) / quantum * quantum;
+    if (count < 2 * quantum || op_is_linear(op)) return gate_batch_host_locked(m->keys[0], op, out, a, b, c, count, nonzero);
+    std::vector<int> rcs(nd, 0);
+    std::vector<std::string> errs(nd);
+    std::vector<std::thread> th;
+    for (int d = 1; d < nd; ++d) {
+        const int64_t g0 = std::min<int64_t>(count, d * per), g = std::min<int64_t>(per, count - g0);
+        if (g <= 0) break;
+        th.emplace_back([&, d, g0, g]() {
+            const size_t off = (size_t)g0 * n1;
+            b200_key *k = m->keys[d];
+            std::lock_guard<std::mutex> lk(k->mu);
+            rcs[d] = gate_batch_host_locked(k, op, out + off, a ? a + off : nullptr, b ? b + off : nullptr, c ? c + off : nullptr,
+                                            g, nonzero ? nonzero + g0 : nullptr);
+            if (rcs[d]) errs[d] = b200_last_error();
+        });
+    }
+    rcs[0] = gate_batch_host_locked(m->keys[0], op, out, a, b, c, std::min(per, count), nonzero);
+    if (rcs[0]) errs[0] = b200_last_error();
+    for (auto &t : th) t.join();
+    for (int d = 0; d < nd; ++d)
+        if (rcs[d]) return fail("device " + std::to_string(m->keys[d]->dk.device) + ": " + errs[d]);
+    return 0;
+}
 static int gate_batch_samples(b200_key *k, int op, LweSample *const *out, const LweSample *const *a,
                               const LweSample *const *b, const LweSample *const *c, int32_t count) {
     const int n = k->dk.n, n1 = n + 1;
@@ -592,7 +787,11 @@ static int gate_batch_samples(b200_key *k, int op, LweSample *const *out, const 
     if (need_a) gather(ha, a);
     if (need_b) gather(hb, b);
     if (need_c) gather(hc, c);
-    if (gate_batch_host_locked(k, op, ho, ha, hb, hc, count, hnz)) return 1;
+    if (b200_multi *m = multi_for_key(k)) {
+        // B200TFHE_DEVICES: the staged batch is cut over the replicas (this key's mutex is held: the replicas'
+        // mutexes are taken by their own threads, device 0's slice by re-entering with the lock already ours)
+        if (multi_gate_batch_locked0(m, op, ho, ha, hb, hc, count, hnz)) return 1;
+    } else if (gate_batch_host_locked(k, op, ho, ha, hb, hc, count, hnz)) return 1;
     for (int32_t i = 0; i < count; ++i) {
         std::memcpy(out[i]->a, ho + (size_t)i * n1, n * sizeof(int32_t));
         out[i]->b = ho[(size_t)i * n1 + n];
@@ -770,6 +969,31 @@ extern "C" int b200_cmux_step_host(b200_key *k, int32_t *acc, int32_t bk_index, 
 extern "C" int b200_extern_product_host(b200_key *k, int32_t *acc, int32_t bk_index, int64_t count) {
     return cmux_host(k, acc, bk_index, 0, 1, count);
 }
+
+// ---- the transform alone (parity tests of the FFT processor replacement) -------------------------------
+static int fft_test_host(int32_t *out, const int32_t *a, const int32_t *b, int mode, int64_t count) {
+    if (count < 0 || count > (1 << 20)) return fail("count out of range");
+    if (count == 0) return 0;
+    if (!out || !a || (mode == 1 && !b)) return fail("NULL polynomial pointer");
+    if (b200_device_count() <= 0) return fail("no CUDA device: libb200tfhe has no CPU fallback");
+    B200_ON_DEVICE(g_device);
+    CK(upload_twiddles());
+    const size_t bytes = (size_t)count * 1024 * sizeof(int32_t);
+    DevBuf da, db, dout;
+    int rc = 0;
+    do {
+        if ((rc = da.ensure(bytes)) || (rc = dout.ensure(bytes)) || (mode == 1 && (rc = db.ensure(bytes)))) break;
+        cudaError_t e = cudaMemcpy(da.p, a, bytes, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess && mode == 1) e = cudaMemcpy(db.p, b, bytes, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = launch_fft_test((const int32_t *)da.p, (const int32_t *)db.p, (int32_t *)dout.p, mode, count, nullptr);
+        if (e == cudaSuccess) e = cudaMemcpy(out, dout.p, bytes, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = fail_cuda("transform test", e);
+    } while (0);
+    da.release(); db.release(); dout.release();
+    return rc;
+}
+extern "C" int b200_fft_roundtrip_host(int32_t *out, const int32_t *a, int64_t count) { return fft_test_host(out, a, nullptr, 0, count); }
+extern "C" int b200_poly_mul_host(int32_t *out, const int32_t *a, const int32_t *b, int64_t count) { return fft_test_host(out, a, b, 1, count); }
 
 // ---- lower-level libtfhe names ----------------------------------------------------------------------
 static b200_key *lookup(std::map<const void *, b200_key *> &m, const void *p) {

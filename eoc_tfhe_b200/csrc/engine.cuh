@@ -66,6 +66,8 @@ cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaS
 // mode 0: acc <- acc + BK_i (x) ((X^a - 1) acc)   mode 1: acc <- BK_i (x) acc
 cudaError_t launch_cmux_test(const DeviceKey &key, int32_t *d_acc, int bk_index, int barai, int mode,
                              int64_t count, cudaStream_t s);
+// the transform alone: mode 0 out = inverse(forward(a)); mode 1 out = a * b mod (X^1024 + 1, 2^32)
+cudaError_t launch_fft_test(const int32_t *d_a, const int32_t *d_b, int32_t *d_out, int mode, int64_t count, cudaStream_t s);
 // linear gates on device batches: out = s*in (+cst on b)
 cudaError_t launch_linear(const DeviceKey &key, int32_t *d_out, const int32_t *d_in, int sign, int32_t cst,
                           int64_t count, cudaStream_t s);
@@ -76,5 +78,6 @@ void set_blind_rotate_variant(int v);  // 0: 64 threads per ciphertext, 1: warp 
 bool experiments_built();              // compiled with -DB200_EXPERIMENTS (round-1 blind-rotation variants 1..8)
 void set_keyswitch_variant(int v);     // 0: chosen by batch size, 1: gather kernel, 2: table-streaming kernel
 cudaError_t measure_fp64_peak(double *tflops);
+cudaError_t measure_int_add_peak(double *tera_adds_per_s);
 
 }  // namespace b200

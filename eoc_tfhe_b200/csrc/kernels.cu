@@ -917,6 +917,53 @@ __global__ void __launch_bounds__(64, UsesTm<FFT>::value ? 1 : 6) k_cmux_test(co
     if (UsesTm<FFT>::value) tm_free_cta(&tm_slot_s);
 }
 
+// The transform alone, for the parity tests that the reference keeps for its FFT processors
+// (libs/tfhe/src/test/lagrangehalfc_test.cpp:16-36 inverse(forward) = identity, :130-218 product = Karatsuba):
+//   mode 0: out = round(inverse(forward(a)) / 512)                      (int32 polynomials mod X^1024 + 1)
+//   mode 1: out = round(inverse(forward(a) * forward(b)) / 512) mod 2^32 (a: small digits, b: Torus32)
+template <class FFT>
+__global__ void __launch_bounds__(64, UsesTm<FFT>::value ? 1 : 6) k_fft_test(const int32_t *__restrict__ a, const int32_t *__restrict__ b,
+                                                                           int32_t *__restrict__ out, int mode, int64_t count) {
+    __shared__ double2 buf[FFT::kBufElemsPerTransform];
+    __shared__ uint32_t tm_slot_s;
+    const int t = threadIdx.x;
+    uint32_t tm = 0;
+    if (UsesTm<FFT>::value) tm = tm_alloc_cta(&tm_slot_s);
+    FFT fft;
+    fft.init(t, tm);
+    for (int64_t item = blockIdx.x; item < count; item += gridDim.x) {
+        const int32_t *pa = a + (size_t)item * kN;
+        double2 x[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) x[r] = make_double2(int_to_double(pa[t + 64 * r]), int_to_double(pa[t + 64 * r + kM]));
+        fft.forward(x, buf, CtaBarrier());
+        __syncthreads();
+        if (mode == 1) {
+            const int32_t *pb = b + (size_t)item * kN;
+            double2 y[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) y[r] = make_double2(int_to_double(pb[t + 64 * r]), int_to_double(pb[t + 64 * r + kM]));
+            fft.forward(y, buf, CtaBarrier());
+            __syncthreads();
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                const double re = fma(x[r].x, y[r].x, -x[r].y * y[r].y), im = fma(x[r].x, y[r].y, x[r].y * y[r].x);
+                x[r] = make_double2(re, im);
+            }
+        }
+        fft.template inverse<false>(x, buf, CtaBarrier());
+        __syncthreads();
+        int32_t *po = out + (size_t)item * kN;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            // products reach 2^50: round to the nearest integer in 64 bits, then reduce mod 2^32
+            po[t + 64 * r] = (int32_t)(uint32_t)(unsigned long long)__double2ll_rn(x[r].x * (1.0 / kM));
+            po[t + 64 * r + kM] = (int32_t)(uint32_t)(unsigned long long)__double2ll_rn(x[r].y * (1.0 / kM));
+        }
+    }
+    if (UsesTm<FFT>::value) tm_free_cta(&tm_slot_s);
+}
+
 // ------------------------------------------------------------------------------------------------
 // key switch, base 4 (basebit 2): tile of TB ciphertexts per CTA, one int4 column group per thread,
 // the three non-zero rows of (i,j) are loaded once per tile and selected by each ciphertext's digit.
@@ -1237,11 +1284,14 @@ static cudaError_t br16_launch(const DeviceKey &key, const BlindRotateArgs &a, c
 cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s) {
     if (a.items <= 0) return cudaSuccess;
     if (a.items > 0x7fffffffLL || key.n + 1 > 640) return cudaErrorInvalidValue;
+    int cur_dev = 0;
+    cudaGetDevice(&cur_dev);
+    const int64_t sms = sm_count_of(cur_dev);   // every threshold below is in units of "ciphertexts per SM"
     {
         // at most one ciphertext per SM: the latency kernel spreads each CMux step over 2l groups
         static int lat = -1;
         if (lat < 0) { const char *e = getenv("B200_LAT"); lat = e ? atoi(e) : 1; }
-        if (lat && a.items <= 148 && br_variant() == 0) {
+        if (lat && a.items <= sms && br_variant() == 0) {
             cudaError_t el = cudaErrorInvalidValue;
             if (key.l == 2 && key.Bgbit == 10) el = lat_launch<2, 10>(key, a, s);
             else if (key.l == 3 && key.Bgbit == 7) el = lat_launch<3, 7>(key, a, s);
@@ -1251,7 +1301,7 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         }
     }
 #ifdef B200_EXPERIMENTS
-    if (br_variant() == 8 && a.items >= 148 * 4 && key.l == 2 && (key.Bgbit == 10 || key.Bgbit == 8)) {
+    if (br_variant() == 8 && a.items >= sms * 4 && key.l == 2 && (key.Bgbit == 10 || key.Bgbit == 8)) {
         // v5: two warps per ciphertext, each a 16-point-per-thread transform engine owning one polynomial
         // (small batches stay on v2: a lone v5 ciphertext takes 5.6 us per step against 4.3 us)
         cudaError_t e5;
@@ -1261,7 +1311,7 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         COUNT_LAUNCH();
         return cudaGetLastError();
     }
-    if (br_variant() == 7 && a.items >= 148 * 4) {
+    if (br_variant() == 7 && a.items >= sms * 4) {
         // v4: v2 with the key delivered through tensor memory (tcgen05.cp), one shared-memory read per CTA
         cudaError_t e4;
         if (key.l == 2 && key.Bgbit == 10) e4 = br4_launch<2, 10, 4>(key, a, s);
@@ -1271,7 +1321,7 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         COUNT_LAUNCH();
         return cudaGetLastError();
     }
-    if (br_variant() >= 2 && br_variant() <= 6 && a.items >= 148 * 4) {
+    if (br_variant() >= 2 && br_variant() <= 6 && a.items >= sms * 4) {
         // v3: accumulators in tensor memory; variant = 2: 6 groups x 1 ciphertext, 3: 4 groups x 2 ciphertexts,
         // 4: 5 x 1, 5: 4 x 1, 6: 3 x 2  (small batches keep the one-group-per-CTA latency path below)
         const int v = br_variant();
@@ -1293,7 +1343,7 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
     if (br_variant() == 1) {
         // 8 ciphertexts per CTA (one CTA per SM, one key read per 8 ciphertexts) once the batch fills
         // the GPU that way, otherwise one warp per CTA so that small batches spread over all SMs.
-        const bool wide16 = a.items >= 148 * 4;
+        const bool wide16 = a.items >= sms * 4;
         cudaError_t e16;
 #define BR16_LAUNCH(L_, B_) e16 = wide16 ? br16_launch<L_, B_, 8>(key, a, s) : br16_launch<L_, B_, 1>(key, a, s)
         if (key.l == 2 && key.Bgbit == 10) BR16_LAUNCH(2, 10);
@@ -1307,7 +1357,7 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         return cudaGetLastError();
     }
 #endif
-    if (br_variant() == 11 && a.items > 148 * 4 && key.l == 2 && key.Bgbit == 10) {
+    if (br_variant() == 11 && a.items > sms * 4 && key.l == 2 && key.Bgbit == 10) {
         // "tms": single transforms, accumulators in tensor memory for every row, 6 / 7 / 8 groups per SM
         static int tmg = -1;
         if (tmg < 0) { const char *ev = getenv("B200_TM_G"); tmg = ev ? atoi(ev) : 8; }
@@ -1318,7 +1368,7 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         COUNT_LAUNCH();
         return cudaGetLastError();
     }
-    if (br_variant() == 10 && a.items > 148 * 4) {
+    if (br_variant() == 10 && a.items > sms * 4) {
         // "tmacc": the tm kernel with the spectral accumulators parked in tensor memory between row pairs
         cudaError_t et;
         static int tmg = -1;
@@ -1335,7 +1385,7 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         COUNT_LAUNCH();
         return cudaGetLastError();
     }
-    if (br_variant() == 9 && a.items > 148 * 4) {
+    if (br_variant() == 9 && a.items > sms * 4) {
         // "tm": the warp-local exchanges of every transform and the per-thread roots in tensor memory
         cudaError_t et;
         static int tmg = -1;   // ciphertexts per CTA at l = 2 (A/B knob: B200_TM_G=4|5|6)
@@ -1353,14 +1403,14 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
     // More than one ciphertext per SM: multi-ciphertext CTAs on a balanced grid (br_launch_st).  Measured at
     // l = 2 (ms, G=1 x 3 CTAs per SM / G=4 / G=6): 296 items 2.39 / 2.29 / 2.66; 591: 4.69 / 3.44 / 3.73;
     // 600: - / 5.49 / 4.74; 887: - / 6.48 / 4.92.
-    const bool wide = a.items > 148;
+    const bool wide = a.items > sms;
     cudaError_t e;
     // l = 2: six groups per CTA (12 warps, 168 registers, 3-stage ring) are 1.9 % faster than four (8 warps,
     // 246 registers, 7 stages); at l = 3 they are 3 % slower (636.6 vs 617.2 ms per 65,536).  B200_G6=0: four.
     static int g6 = -1;
     if (g6 < 0) { const char *ev = getenv("B200_G6"); g6 = ev ? atoi(ev) : 1; }
 #define BR_LAUNCH(L_, B_) e = wide ? br_launch<L_, B_, 4>(key, a, s) : br_launch<L_, B_, 1>(key, a, s)
-    if (g6 && a.items > 148 * 4 && key.l == 2 && key.Bgbit == 10) {
+    if (g6 && a.items > sms * 4 && key.l == 2 && key.Bgbit == 10) {
         // A wave of the six-group kernel takes about as long with four groups per CTA as with six (4.74 vs
         // 4.92 ms), a wave of the four-group kernel 3.44 ms (2.3 ms at two per CTA) and the latency kernel
         // 1.35 ms: when what is left after whole six-group waves fits one narrower wave, it goes there.
@@ -1456,12 +1506,28 @@ cudaError_t launch_cmux_test(const DeviceKey &key, int32_t *d_acc, int bk_index,
     return cudaGetLastError();
 }
 
+cudaError_t launch_fft_test(const int32_t *d_a, const int32_t *d_b, int32_t *d_out, int mode, int64_t count, cudaStream_t s) {
+    if (count <= 0) return cudaSuccess;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const int v = br_variant_raw();
+    if ((v >= 9 && v <= 11) || v == kVarAuto)
+        k_fft_test<FftTm><<<(unsigned)std::min<int64_t>(count, sm_count_of(dev)), 64, 0, s>>>(d_a, d_b, d_out, mode, count);
+    else
+        k_fft_test<FftSmem><<<(unsigned)std::min<int64_t>(count, 148 * 6), 64, 0, s>>>(d_a, d_b, d_out, mode, count);
+    COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
 static std::atomic<int> g_ks_variant{-1};
 void set_keyswitch_variant(int v) { g_ks_variant.store(v); }
 cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaStream_t s) {
     if (a.items <= 0) return cudaSuccess;
     if (key.ks_basebit != 2 || key.ks_t != 8) return cudaErrorInvalidValue;  // both reference sets: t=8, base 4
     const int Nin = key.N * key.k;
+    int cur_dev = 0;
+    cudaGetDevice(&cur_dev);
+    const int64_t sms = sm_count_of(cur_dev);
     // large batches: table streamed once per 64 (48) samples through a TMA-fed shared-memory ring
     int ks_sel = g_ks_variant.load();   // 0: by batch size, 1: gather kernel, 2: streaming kernel
     if (ks_sel < 0) { const char *e = getenv("B200_KS"); ks_sel = e ? atoi(e) : 0; g_ks_variant.store(ks_sel); }
@@ -1472,8 +1538,8 @@ cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaS
         // 16 samples per group -> 8 warps, 43 ms; digit pairs with a 16-way branch -> 34-49 ms; this -> 26 ms).
         // Batches that cannot fill 148 CTAs of 64 samples use CTAs of 32 (two per SM) down to 2,960 samples (below that the gather kernel is as fast).
         const int64_t per_cta = small ? 64 : 40;
-        const bool full = a.items >= 148 * per_cta;
-        if (ks_sel == 2 || a.items >= 148 * 20) {
+        const bool full = a.items >= sms * per_cta;
+        if (ks_sel == 2 || a.items >= sms * 20) {
             cudaError_t e = small ? (full ? ks2_launch<64, 8, 8, 2>(key, a, s) : ks2_launch<64, 4, 8, 2>(key, a, s))
                                   : (full ? ks2_launch<96, 5, 8, 2>(key, a, s) : ks2_launch<96, 3, 8, 2>(key, a, s));
             if (e != cudaSuccess) return e;
@@ -1484,7 +1550,7 @@ cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaS
     const int64_t tiles = (a.items + kKsTile - 1) / kKsTile;
     // enough CTAs to fill 148 SMs several times over; small batches split the i range instead
     int nsplit = 1;
-    while (tiles * nsplit < 148 * 4 && nsplit < 64) nsplit *= 2;
+    while (tiles * nsplit < sms * 4 && nsplit < 64) nsplit *= 2;
     const int i_per_split = (Nin + nsplit - 1) / nsplit;
     const int threads = ((key.ks_stride / 4) + 31) / 32 * 32;
     if (threads > 160) return cudaErrorInvalidValue;
@@ -1559,6 +1625,56 @@ cudaError_t measure_fp64_peak(double *tflops) {
     cudaEventDestroy(e1);
     cudaFree(sink);
     *tflops = best;
+    return e;
+}
+
+// int32 add issue peak (roofline denominator of the key switch, which is a stream of 32-bit subtractions):
+// 16 independent chains per thread, x -= y with y changing per iteration so that nothing folds.
+__global__ void __launch_bounds__(256) k_int_add_peak(int32_t *sink, int iters, int32_t seed) {
+    int32_t a[16];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) a[r] = seed + threadIdx.x * 17 + r;
+    int32_t y = seed ^ 0x5bd1e995, z = seed + 12345;
+#pragma unroll 1
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+#pragma unroll
+            for (int r = 0; r < 16; r += 2) { a[r] -= y; a[r + 1] -= z; }
+        }
+        y += z;    // two more adds per 64: not counted
+        z ^= i;
+    }
+    int32_t r = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) r ^= a[k];
+    if (r == 0x7fffffff) sink[0] = r;
+}
+cudaError_t measure_int_add_peak(double *tera_adds_per_s) {
+    int32_t *sink = nullptr;
+    cudaError_t e = cudaMalloc(&sink, 4);
+    if (e != cudaSuccess) return e;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int blocks = 148 * 8, iters = 4096;
+    double best = 0;
+    for (int rep = 0; rep < 4; ++rep) {
+        cudaEventRecord(e0);
+        k_int_add_peak<<<blocks, 256>>>(sink, iters, 12345 + rep);
+        COUNT_LAUNCH();
+        cudaEventRecord(e1);
+        e = cudaEventSynchronize(e1);
+        if (e != cudaSuccess) break;
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double adds = 64.0 * iters * 256.0 * blocks;
+        if (rep > 0 && ms > 0) best = fmax(best, adds / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(sink);
+    *tera_adds_per_s = best;
     return e;
 }
 

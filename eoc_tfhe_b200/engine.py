@@ -286,6 +286,13 @@ def fp64_peak_tflops(device=0):
     return v.value
 
 
+def int32_add_peak(device=0):
+    """32-bit integer add throughput of the device measured by the library's chain kernel (10^12 adds/s)."""
+    v = C.c_double()
+    _lib.check(_lib.load().b200_int32_add_peak(int(device), C.byref(v)))
+    return v.value
+
+
 def set_blind_rotate_kernel(variant):
     """12 / "auto" (default): the fastest kernel per launch ("tmacc" for wide batches at l = 2, else "v2" and the
     latency kernel); 0 / "v2": shared-memory transforms; 9 / "tm", 10 / "tmacc", 11 / "tms": tensor-memory transforms
@@ -293,6 +300,22 @@ def set_blind_rotate_kernel(variant):
     B200_EXPERIMENTS build)."""
     v = {"v2": 0, "w16": 1, "v3g6": 2, "v3c2": 3, "v3g5": 4, "v3g4": 5, "v3g3c2": 6, "v4": 7, "v5": 8, "tm": 9, "tmacc": 10, "tms": 11, "auto": 12}.get(variant, variant)
     _lib.check(_lib.load().b200_set_blind_rotate_kernel(int(v)))
+
+
+def fft_roundtrip(a):
+    """inverse(forward(a)) of the selected kernel's transform on int32 polynomials [count][1024]: the identity."""
+    a = _np_i32(a)
+    out = np.empty_like(a)
+    _lib.check(_lib.load().b200_fft_roundtrip_host(_ptr(out), _ptr(a), a.shape[0]))
+    return out
+
+
+def poly_mul(a, b):
+    """a * b mod (X^1024 + 1, 2^32) through the transform; a small (gadget digits), b any Torus32."""
+    a, b = _np_i32(a), _np_i32(b)
+    out = np.empty_like(a)
+    _lib.check(_lib.load().b200_poly_mul_host(_ptr(out), _ptr(a), _ptr(b), a.shape[0]))
+    return out
 
 
 def experiments_built():

@@ -66,6 +66,13 @@ SIGNATURES = {
     "b200_wire_write_samples": (C.c_int, [_VP, C.c_size_t, C.c_int32, C.c_int64, _VP, _VP]),
     "b200_set_blind_rotate_kernel": (C.c_int, [C.c_int]),
     "b200_experiments_built": (C.c_int, []),
+    "b200_int32_add_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
+    "b200_multi_create": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p)]),
+    "b200_multi_free": (None, [C.c_void_p]),
+    "b200_multi_device_count": (C.c_int, [C.c_void_p]),
+    "b200_multi_gate_batch_host": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
+    "b200_fft_roundtrip_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
+    "b200_poly_mul_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
     "b200_set_keyswitch_kernel": (C.c_int, [C.c_int]),
     "bootsGate_batch": (C.c_int, [C.c_int, _VP, _VP, _VP, _VP, C.c_int32, _VP]),
     # eoc evaluation-side entry points (csrc/eoc_abi.cpp); strings come back as new[] pointers

@@ -241,12 +241,34 @@ int  b200_gate_batch_host(b200_key *key, int op, int32_t *out, const int32_t *a,
 int  b200_gate_batch_dev(b200_key *key, int op, int32_t *d_out, const int32_t *d_a,
                          const int32_t *d_b, const int32_t *d_c, int64_t count, void *stream);
 
+/* Several devices behind one handle (north_star: gates partitioned over the GPUs of a box, cloud key replicated).
+ * b200_multi_create replicates `key` (which stays owned by the caller and must outlive the handle) onto the listed
+ * devices -- devices[0] must be the key's own device; devices == NULL takes the first ndev devices of the box
+ * (ndev <= 0: all), the key's own first -- by device-to-device copies of the two resident blobs.
+ * b200_multi_gate_batch_host cuts a host batch into contiguous slices of whole blind-rotation waves, one per
+ * device, each evaluated by its own host thread through b200_gate_batch_host's path; results are identical to the
+ * single-device call word for word.  The drop-in bootsGate_batch does the same when the environment variable
+ * B200TFHE_DEVICES is "all" or a device count. */
+typedef struct b200_multi b200_multi;
+int  b200_multi_create(b200_key *key, const int32_t *devices, int32_t ndev, b200_multi **out);
+void b200_multi_free(b200_multi *m);
+int  b200_multi_device_count(const b200_multi *m);
+int  b200_multi_gate_batch_host(b200_multi *m, int op, int32_t *out, const int32_t *a, const int32_t *b,
+                                const int32_t *c, int64_t count);
+
 /* Pieces of the path, for parity tests and for callers that hold extracted samples. */
 /* u[count][N+1] = tfhe_bootstrap_woKS_FFT(x[count][n+1], mu)       (fft.cpp:169-200) */
 int  b200_bootstrap_woks_host(b200_key *key, int32_t *u, const int32_t *x, int32_t mu, int64_t count);
 /* out[count][n+1] = lweKeySwitch(u[count][N+1]); nonzero_digits[count] optional (may be NULL) */
 int  b200_keyswitch_host(b200_key *key, int32_t *out, const int32_t *u, int32_t *nonzero_digits, int64_t count);
 int  b200_keyswitch_dev (b200_key *key, int32_t *d_out, const int32_t *d_u, int64_t count, void *stream);
+/* The negacyclic transform alone (replaces the reference's FFT processors, fft_processor_spqlios.cpp:38-115), with
+ * the checks the reference keeps for them (src/test/lagrangehalfc_test.cpp:16-36, 130-218).  Polynomials are
+ * int32 [count][1024] mod X^1024 + 1; the transform is the one the selected blind-rotation kernel uses.
+ *   b200_fft_roundtrip_host: out = round(inverse(forward(a)) / 512)         -- the identity on any int32 input
+ *   b200_poly_mul_host:      out = a * b mod 2^32, a small (|a_j| <= 512: gadget digits), b any Torus32 */
+int  b200_fft_roundtrip_host(int32_t *out, const int32_t *a, int64_t count);
+int  b200_poly_mul_host(int32_t *out, const int32_t *a, const int32_t *b, int64_t count);
 /* One CMux step: acc[count][k+1][N] <- acc + BK_i (x) ((X^barai - 1) * acc)   (fft.cpp:67-76).
  * With barai == 0 the accumulator is returned unchanged, as tfhe_blindRotate_FFT skips (fft.cpp:101). */
 int  b200_cmux_step_host(b200_key *key, int32_t *acc, int32_t bk_index, int32_t barai, int64_t count);
@@ -352,6 +374,9 @@ int  b200_timing_drain(b200_key *key, double sum_ms[2], int32_t *calls);
 /* FP64 FMA throughput of `device` measured by a DFMA-chain kernel (TFLOP/s): the roofline
  * denominator bench.py reports the blind rotation against. */
 int  b200_fp64_peak_tflops(int device, double *tflops);
+/* 32-bit integer add throughput of `device` measured by a chain kernel (10^12 adds/s): the roofline denominator of
+ * the key switch, whose work is 6,144 row subtractions of n+1 words per sample (lwe-keyswitch-functions.cpp:114-129). */
+int  b200_int32_add_peak(int device, double *tera_adds_per_s);
 /* Blind-rotation kernel used by subsequent calls: 0 = 64 threads per ciphertext, accumulators in
  * registers (default); 1 = one warp per ciphertext, 16-point transforms, accumulators in tensor memory
  * (tcgen05.ld/st); 2..6 = the 64-thread layout with accumulators in tensor memory (2: 6 groups per SM,

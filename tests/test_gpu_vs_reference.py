@@ -167,3 +167,36 @@ def test_all_gates_decrypt_like_reference(keys):
     assert np.array_equal(ck.gate(GateOp.COPY, a), a)
     one = ck.gate(GateOp.CONST1, out=np.empty_like(a))
     assert np.all(one[:, :-1] == 0) and np.all(one[:, -1] == 1 << 29)
+
+
+@pytest.mark.skipif(not reflib.available("nayuki-portable"), reason="oracle/_ref/libtfhe-nayuki-portable.so not built")
+def test_against_nayuki_portable_processor():
+    """The FFT processor eoc actually ships (config.yml:21-25, fft_processors/nayuki/fft_processor_nayuki.cpp:34-86) as
+    the second oracle: one external product within 2 LSB of its FP64 result and of the exact product, one CMux step
+    within 2 LSB, gates decrypt to the same bits -- on a key generated by that build."""
+    from eoc_tfhe_b200 import CloudKey, GateOp
+    ref = reflib.RefLib("nayuki-portable")
+    rk = ref.keygen(80, seed=77)
+    ck = CloudKey.from_libtfhe(rk.cloud_ptr)
+    try:
+        rng = np.random.default_rng(9)
+        acc = rng.integers(-2**31, 2**31, size=(3, 2, rk.N), dtype=np.int64).astype(np.int32)
+        got = ck.extern_product(acc, 4)
+        for g in range(acc.shape[0]):
+            for want in (rk.extern_product_fft(acc[g], 4), rk.extern_product_exact(acc[g], 4)):
+                d = np.abs((got[g].astype(np.int64) - want.astype(np.int64) + 2**31) % 2**32 - 2**31)
+                assert d.max() <= 2, d.max()
+        got = ck.cmux_step(acc, 7, 1531)
+        for g in range(acc.shape[0]):
+            want = rk.cmux_step(acc[g], 7, 1531)
+            d = np.abs((got[g].astype(np.int64) - want.astype(np.int64) + 2**31) % 2**32 - 2**31)
+            assert d.max() <= 2, d.max()
+        a_bits, b_bits = rng.integers(0, 2, size=16), rng.integers(0, 2, size=16)
+        a, b = rk.encrypt_bits(a_bits), rk.encrypt_bits(b_bits)
+        out = ck.gate(GateOp.NAND, a, b)
+        ref_out, _ = rk.gate("NAND", a, b)
+        assert np.array_equal(rk.decrypt_bits(out), 1 - (a_bits & b_bits))
+        assert np.array_equal(rk.decrypt_bits(ref_out), rk.decrypt_bits(out))
+        assert np.array_equal(ck.keyswitch(rk.bootstrap_woks(a)), rk.keyswitch(rk.bootstrap_woks(a))[0])   # bit-exact
+    finally:
+        ck.close()

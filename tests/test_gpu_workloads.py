@@ -79,38 +79,70 @@ def test_million_gates_bit_exact(p80):
         assert torch.equal(got, want.to(torch.int32)), name
         total += per
         if name not in sample:
-            sample[name] = (a[:24].cpu().numpy(), b[:24].cpu().numpy(), c[:24].cpu().numpy(), got[:24].cpu().numpy())
+            ns = 1024
+            sample[name] = (a[:ns].cpu().numpy(), b[:ns].cpu().numpy(), c[:ns].cpu().numpy(), got[:ns].cpu().numpy())
     assert total >= 10 ** 6
-    # the reference's own gates on a sample of exactly these inputs decrypt to the same bits
+    # libtfhe's own gates (unmodified reference, one gate stream per host core) on 1,024 of exactly these inputs per
+    # gate type -- 11,264 reference gates -- decrypt to the same bits
     for name, (a, b, c, got) in sample.items():
         ref_out, _ = rk.gate_mt(name, a, b, c if name == "MUX" else None)
         assert np.array_equal(rk.decrypt_bits(ref_out), got), name
 
 
-def test_output_noise_variance_within_5_percent(p80):
-    """Phase error of NAND outputs (after key switch): variance over 32,768 GPU gates vs 16,384 reference
-    gates on the same key and input pool; the north_star bound is 5 %."""
-    import torch
+def _variance_check(rk, ck, op, n_gpu, n_ref, seed):
+    """Phase error of gate outputs (after key switch): variance over n_gpu GPU gates against n_ref gates of the
+    unmodified reference on the same key and input pool; the north_star bound is 5 %."""
     from eoc_tfhe_b200 import GateOp
-    rk, ck = p80
-    rng = np.random.default_rng(31)
+    rng = np.random.default_rng(seed)
     pool_bits = rng.integers(0, 2, size=2048).astype(np.int32)
     pool = rk.encrypt_bits(pool_bits)
-    ia, ib = rng.integers(0, 2048, size=32768), rng.integers(0, 2048, size=32768)
-    a, b = pool[ia], pool[ib]
-    want = 1 - (pool_bits[ia] & pool_bits[ib])
+    ia, ib, ic = (rng.integers(0, 2048, size=n_gpu) for _ in range(3))
+    a, b, c = pool[ia], pool[ib], pool[ic]
+    if op == "MUX":     # boot-gates.cpp:329-370: two rotations, their sum + (0, 1/8), ONE key switch
+        want = np.where(pool_bits[ia] > 0, pool_bits[ib], pool_bits[ic])
+        out = ck.gate(GateOp.MUX, a, b, c)
+        ref_out, _ = rk.gate_mt("MUX", a[:n_ref], b[:n_ref], c[:n_ref])
+    else:
+        want = 1 - (pool_bits[ia] & pool_bits[ib])
+        out = ck.gate(GateOp.NAND, a, b)
+        ref_out, _ = rk.gate_mt("NAND", a[:n_ref], b[:n_ref])
     mu = np.where(want > 0, 1 << 29, -(1 << 29)).astype(np.int64)
-    out = ck.gate(GateOp.NAND, a, b)
     err_gpu = rk.phase(out).astype(np.int64) - mu
-    nref = 16384
-    ref_out, _ = rk.gate_mt("NAND", a[:nref], b[:nref])
-    err_ref = rk.phase(ref_out).astype(np.int64) - mu[:nref]
+    err_ref = rk.phase(ref_out).astype(np.int64) - mu[:n_ref]
     v_gpu, v_ref = float(np.var(err_gpu)), float(np.var(err_ref))
     # the mean is a property of the key (sum of the key-switch rows' fixed noise), so it is compared with
     # the reference's mean, not with zero
-    assert abs(np.mean(err_gpu) - np.mean(err_ref)) < 4 * np.sqrt(v_gpu / len(err_gpu) + v_ref / nref)
-    assert abs(v_gpu / v_ref - 1.0) < 0.05, (v_gpu, v_ref)
-    assert np.abs(err_gpu).max() < 2 ** 28                                   # far from the 1/8 decision margin... (1/16)
+    assert abs(np.mean(err_gpu) - np.mean(err_ref)) < 4 * np.sqrt(v_gpu / len(err_gpu) + v_ref / n_ref)
+    assert abs(v_gpu / v_ref - 1.0) < 0.05, (op, v_gpu, v_ref)
+    assert np.abs(err_gpu).max() < 2 ** 28                                   # far from the 1/8 decision margin
+
+
+def test_output_noise_variance_within_5_percent(p80):
+    """NAND at the 80-bit set: 32,768 GPU gates vs 16,384 reference gates."""
+    rk, ck = p80
+    _variance_check(rk, ck, "NAND", 32768, 16384, 31)
+
+
+def test_output_noise_variance_mux_p80(p80):
+    """MUX at the 80-bit set (sum of two extracted samples before one key switch): 16,384 GPU vs 8,192 reference."""
+    rk, ck = p80
+    _variance_check(rk, ck, "MUX", 16384, 8192, 32)
+
+
+@pytest.fixture(scope="module")
+def p128():
+    from eoc_tfhe_b200 import CloudKey
+    rk = reflib.RefLib().keygen(128, seed=987)
+    ck = CloudKey.from_libtfhe(rk.cloud_ptr)
+    yield rk, ck
+    ck.close()
+
+
+@pytest.mark.parametrize("op", ["NAND", "MUX"])
+def test_output_noise_variance_p128(p128, op):
+    """The n = 630, l = 3 kernels (k_blind_rotate<3,7,...>, 40-sample key-switch CTAs): 16,384 GPU vs 8,192 reference."""
+    rk, ck = p128
+    _variance_check(rk, ck, op, 16384, 8192, 33 if op == "NAND" else 34)
 
 
 @pytest.mark.parametrize("builder", ["full_adder", "full_adder_mux"])
@@ -516,3 +548,30 @@ def test_wide_circuit_level_equals_gate_batch(p80):
     assert np.array_equal(wires[3 * m:4 * m], ck.gate(GateOp.XOR, tx, ty).cpu().numpy())
     assert np.array_equal(wires[4 * m:], ck.gate(GateOp.MUX, tx[:m // 2], ty[:m // 2], tz[:m // 2]).cpu().numpy())
     assert np.array_equal(rk.decrypt_bits(wires[3 * m:4 * m]), bits[0] ^ bits[1])
+
+
+def test_multi_device_entry_equals_single_device(p80):
+    """b200_multi_gate_batch_host (one key replica and one host thread per device, contiguous slices) against
+    b200_gate_batch_host on one device: word for word, NAND and MUX, a ragged count."""
+    import ctypes as C
+    from eoc_tfhe_b200 import GateOp, lib as _lib
+    L = _lib.load()
+    if L.b200_device_count() < 2:
+        pytest.skip("needs at least 2 GPUs (gpurun --gpus 2)")
+    rk, ck = p80
+    rng = np.random.default_rng(5)
+    n1 = rk.n + 1
+    count = 148 * 6 * 5 + 77
+    a, b, c = (rng.integers(-2**31, 2**31, size=(count, n1), dtype=np.int64).astype(np.int32) for _ in range(3))
+    m = C.c_void_p()
+    _lib.check(L.b200_multi_create(ck._h, None, 0, C.byref(m)))
+    try:
+        assert L.b200_multi_device_count(m) == L.b200_device_count()
+        for op, cc in ((GateOp.NAND, None), (GateOp.MUX, c)):
+            want = ck.gate(op, a, b, cc) if cc is not None else ck.gate(op, a, b)
+            got = np.empty_like(a)
+            _lib.check(L.b200_multi_gate_batch_host(m, int(op), got.ctypes.data, a.ctypes.data, b.ctypes.data,
+                                                    cc.ctypes.data if cc is not None else None, count))
+            assert np.array_equal(got, want), op
+    finally:
+        L.b200_multi_free(m)
