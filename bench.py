@@ -494,7 +494,6 @@ def main_b200(args):
         }
         if world > 1:
             line["sharded_equal"] = sharded_equal
-            line["nccl"] = nccl_log_relay(nccl_path, world)
         if config5:
             line["config5"] = config5
         if p128:
@@ -512,11 +511,14 @@ def main_b200(args):
             one = run_ref_bench(1, 16)
             if one:
                 line["latency"]["cpu_single_gate_ms"] = one["ms_per_gate_per_thread"]
-        print(json.dumps(line), flush=True)
     ck.close()
     if world > 1:
         dist.barrier()
-        dist.destroy_process_group()
+        dist.destroy_process_group()      # NCCL flushes its log file when the communicator goes
+    if rank == 0:
+        if world > 1:
+            line["nccl"] = nccl_log_relay(nccl_path, world)
+        print(json.dumps(line), flush=True)
     return 0
 
 
