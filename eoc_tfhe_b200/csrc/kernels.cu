@@ -606,19 +606,16 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
             const int ev = q * ((L + 1) / 2) + p / 2;
             if (ev > 0) bar();   // every thread of the group has read the previous transforms' exchange buffers
             const int shift = 32 - (p + 1) * BGBIT;
+            // digits as exact doubles, registers 4..7 pre-twisted by the level-0 root on the integer side
             double2 xa[8];
-#pragma unroll
-            for (int r = 0; r < 8; ++r)
-                xa[r] = make_double2(digit_to_double<BGBIT>(dv[r], shift), digit_to_double<BGBIT>(dv[r + 8], shift));
+            digits_pretwisted<BGBIT>(xa, dv, shift);
             if (p + 1 < L) {
                 double2 xb[8];
-#pragma unroll
-                for (int r = 0; r < 8; ++r)
-                    xb[r] = make_double2(digit_to_double<BGBIT>(dv[r], shift - BGBIT), digit_to_double<BGBIT>(dv[r + 8], shift - BGBIT));
-                fft.forward2(xa, xb, bufs, bufs + kBuf, bar);
+                digits_pretwisted<BGBIT>(xb, dv, shift - BGBIT);
+                fft.template forward2<true>(xa, xb, bufs, bufs + kBuf, bar);
                 mac_event(ev, xa, &xb, q * L + p);
             } else {
-                fft.forward(xa, bufs, bar);
+                fft.template forward<true>(xa, bufs, bar);
                 mac_event(ev, xa, nullptr, q * L + p);
             }
         }

@@ -117,6 +117,29 @@ __device__ __forceinline__ void fwd_radix8(double2 (&x)[8], const RootSet &w) {
     ct_bfly_i(x[6], x[7], w.D);
 }
 
+// First pass of a forward transform whose inputs are gadget digits: the root of level 0 is e^{i pi/4} (tan = 1), so
+// its twist w = v (1 + i) = (v.x - v.y, v.x + v.y) is an INTEGER sum that the caller forms before converting to
+// double (digits_pretwisted): x[4..7] arrive as w, and the level costs 4 DFMA per butterfly instead of 6.
+__device__ __forceinline__ void fwd_radix8_first_pretwisted(double2 (&x)[8]) {
+    const double c = c_tw.p1.A.x;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const double ur = x[r].x, ui = x[r].y, wr = x[r + 4].x, wi = x[r + 4].y;
+        x[r].x = fma(c, wr, ur);
+        x[r].y = fma(c, wi, ui);
+        x[r + 4].x = fma(-c, wr, ur);
+        x[r + 4].y = fma(-c, wi, ui);
+    }
+    ct_bfly(x[0], x[2], c_tw.p1.B);
+    ct_bfly(x[1], x[3], c_tw.p1.B);
+    ct_bfly_i(x[4], x[6], c_tw.p1.B);
+    ct_bfly_i(x[5], x[7], c_tw.p1.B);
+    ct_bfly(x[0], x[1], c_tw.p1.C);
+    ct_bfly_i(x[2], x[3], c_tw.p1.C);
+    ct_bfly(x[4], x[5], c_tw.p1.D);
+    ct_bfly_i(x[6], x[7], c_tw.p1.D);
+}
+
 __device__ __forceinline__ void inv_radix8(double2 (&x)[8], const RootSet &w) {
     gs_bfly(x[0], x[1], w.C);
     gs_bfly_i(x[2], x[3], w.C);
@@ -250,6 +273,23 @@ __device__ __forceinline__ double digit_to_double(uint32_t v, int shift) {
     constexpr double kBias = 4503599627370496.0 + (double)(1u << (BGBIT - 1));  // 2^52 + Bg/2
     return __hiloint2double(0x43300000, (int)((v >> shift) & MASK)) - kBias;
 }
+// The eight complex inputs of a forward transform from the 16 decomposition words of a thread (coefficients
+// t + 64 rr, rr = 0..15; x[r] = (digit rr = r, digit rr = r + 8)), registers 4..7 already twisted by the level-0
+// root: (d1 - d2, d1 + d2) with d = field - Bg/2, i.e. (f1 - f2, f1 + f2 - Bg) -- exact small integers, converted
+// like int_to_double.  For fwd_radix8_first_pretwisted.
+template <int BGBIT>
+__device__ __forceinline__ void digits_pretwisted(double2 (&x)[8], const uint32_t (&dv)[16], const int shift) {
+    constexpr uint32_t MASK = (1u << BGBIT) - 1;
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+        x[r] = make_double2(digit_to_double<BGBIT>(dv[r], shift), digit_to_double<BGBIT>(dv[r + 8], shift));
+#pragma unroll
+    for (int r = 4; r < 8; ++r) {
+        const int32_t f1 = (int32_t)((dv[r] >> shift) & MASK), f2 = (int32_t)((dv[r + 8] >> shift) & MASK);
+        x[r] = make_double2(int_to_double(f1 - f2), int_to_double(f1 + f2 - (int32_t)(1u << BGBIT)));
+    }
+}
+
 // round-to-nearest of x*scale to an integer, reduced mod 2^32 (|x*scale| < 2^51)
 __device__ __forceinline__ int32_t round_scaled_to_torus(double x, double scale) {
     return __double2loint(fma(x, scale, 6755399441055744.0));  // 1.5 * 2^52

@@ -280,9 +280,9 @@ struct FftTm {
     }
 
     // coefficients (x[r] = z_{t+64r}) -> evaluations in the P3b layout
-    template <class Barrier>
+    template <bool PRE = false, class Barrier>
     __device__ __forceinline__ void forward(double2 (&x)[8], double2 *buf, const Barrier &bar) const {
-        fwd_radix8(x, c_tw.p1);
+        if (PRE) fwd_radix8_first_pretwisted(x); else fwd_radix8(x, c_tw.p1);
 #pragma unroll
         for (int r = 0; r < 8; ++r) buf[tm_slot(t + 64 * r)] = x[r];
         double rt[8];
@@ -317,14 +317,15 @@ struct FftTm {
     // nobody still reads them (group barrier after the previous transform's reads).
     struct NoMid { __device__ __forceinline__ void operator()() const {} };
     // mid(): called when xa is complete and xb's last exchange is in flight (the caller's spectral MAC of xa)
-    template <class Barrier, class Mid = NoMid>
+    // PRE: xa[4..7], xb[4..7] arrive twisted by the level-0 root (digits_pretwisted)
+    template <bool PRE = false, class Barrier, class Mid = NoMid>
     __device__ __forceinline__ void forward2(double2 (&xa)[8], double2 (&xb)[8], double2 *bufa, double2 *bufb,
                                              const Barrier &bar, const Mid &mid = Mid()) const {
         const uint32_t tma = tm, tmb = tm + kTmColExB;
-        fwd_radix8(xa, c_tw.p1);
+        if (PRE) fwd_radix8_first_pretwisted(xa); else fwd_radix8(xa, c_tw.p1);
 #pragma unroll
         for (int r = 0; r < 8; ++r) bufa[tm_slot(t + 64 * r)] = xa[r];
-        fwd_radix8(xb, c_tw.p1);
+        if (PRE) fwd_radix8_first_pretwisted(xb); else fwd_radix8(xb, c_tw.p1);
 #pragma unroll
         for (int r = 0; r < 8; ++r) bufb[tm_slot(t + 64 * r)] = xb[r];
         double rt[8], r3[8];
