@@ -427,6 +427,18 @@ def main_b200(args):
             ck.gate(GateOp.NAND, one_a, one_b, out=one_o)
             samples.append((time.perf_counter() - t0) * 1e3)
         lat_ms = sorted(samples)[len(samples) // 2]
+        # the same call from 4 host threads at once (one gate stream per thread, like libtfhe's users): lanes of the key
+        from concurrent.futures import ThreadPoolExecutor
+
+        def stream(_):
+            xa, xb, xo = one_a.copy(), one_b.copy(), one_o.copy()
+            for _ in range(40):
+                ck.gate(GateOp.NAND, xa, xb, out=xo)
+        with ThreadPoolExecutor(max_workers=4) as ex:
+            list(ex.map(stream, range(4)))
+            t0 = time.perf_counter()
+            list(ex.map(stream, range(4)))
+            lat_threads4 = 160 / (time.perf_counter() - t0)
 
     # ---- BASELINE configs[3] on one GPU: 2^18 bootsMUX at the 128-bit set (n=630, l=3, Bgbit=7), incl. key switch
     p128 = None
@@ -475,7 +487,8 @@ def main_b200(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * count * n1 * 4, "d2h_bytes_per_step": count * n1 * 4,
                     "steps": args.steps, "api": "b200_gate_batch_host (pinned host buffers)", "matches_device_path": same},
             "gpu_launches": int(launches),
-            "latency": {"single_gate_ms": lat_ms, "api": "b200_gate_batch_host, count = 1 (H2D, two kernels, D2H, synchronous)"},
+            "latency": {"single_gate_ms": lat_ms, "api": "b200_gate_batch_host, count = 1 (H2D, two kernels, D2H, synchronous)",
+                        "single_gate_streams_4_host_threads_gates_per_s": lat_threads4},
             "roofline": {"bound": "fp64", "kernel": "k_blind_rotate<2,10,6,4,FftTmAcc>", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
                          "frac": achieved / fp64_peak if fp64_peak else None, "traffic": ncu_traffic("k_blind_rotate"),
                          "ms_per_launch": br, "share_of_step": br / ms_per_step,

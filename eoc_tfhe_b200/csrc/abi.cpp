@@ -93,6 +93,37 @@ static int check_params(const b200_params *p) {
     return 0;
 }
 
+// streams, events: everything of a key object but the resident blobs (also what a lane owns)
+static cudaError_t key_init_runtime(b200_key *k) {
+    cudaError_t e = cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&k->stream_h2d, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&k->stream_d2h, cudaStreamNonBlocking);
+    for (int i = 0; i < b200_key::kSlices && e == cudaSuccess; ++i) {
+        e = cudaEventCreateWithFlags(&k->ev_up[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&k->ev_done[i], cudaEventDisableTiming);
+    }
+    for (int i = 0; i < b200_key::kRing * 3 && e == cudaSuccess; ++i) e = cudaEventCreate(&k->ring[i / 3][i % 3]);
+    if (e == cudaSuccess) e = cudaEventCreate(&k->ev_start);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&k->ev_scratch, cudaEventDisableTiming);
+    return e;
+}
+b200_key *b200_lane_create(b200_key *master) {
+    DeviceGuard dg(master->dk.device);
+    if (dg.err != cudaSuccess) return nullptr;
+    b200_key *l = new (std::nothrow) b200_key();
+    if (!l) return nullptr;
+    l->dk = master->dk;          // the same resident blobs
+    l->owns_blobs = false;
+    l->master = master;
+    l->filled = true;
+    if (key_init_runtime(l) != cudaSuccess) {
+        cudaGetLastError();
+        b200_key_free(l);
+        return nullptr;
+    }
+    return l;
+}
+
 static int key_alloc(const b200_params *p, b200_key **out, int device = -1) {
     if (!out) return fail("out is NULL");
     *out = nullptr;
@@ -117,16 +148,7 @@ static int key_alloc(const b200_params *p, b200_key **out, int device = -1) {
     cudaError_t e = cudaMalloc((void **)&d.bkfft, d.bkfft_bytes);
     if (e == cudaSuccess) { d.bkfft_tm = d.bkfft + bk_elems; d.bkfft16 = d.bkfft + 2 * bk_elems; }
     if (e == cudaSuccess) e = cudaMalloc((void **)&d.ks, d.ks_bytes);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&k->stream_h2d, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&k->stream_d2h, cudaStreamNonBlocking);
-    for (int i = 0; i < b200_key::kSlices && e == cudaSuccess; ++i) {
-        e = cudaEventCreateWithFlags(&k->ev_up[i], cudaEventDisableTiming);
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&k->ev_done[i], cudaEventDisableTiming);
-    }
-    for (int i = 0; i < b200_key::kRing * 3 && e == cudaSuccess; ++i) e = cudaEventCreate(&k->ring[i / 3][i % 3]);
-    if (e == cudaSuccess) e = cudaEventCreate(&k->ev_start);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&k->ev_scratch, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = key_init_runtime(k);
     if (e == cudaSuccess) e = upload_twiddles();
     if (e != cudaSuccess) {
         fail_cuda("key allocation", e);
@@ -194,10 +216,12 @@ extern "C" void b200_key_free(b200_key *k) {
         for (auto *m : {&g_by_cloud, &g_by_bkfft, &g_by_ks})
             for (auto it = m->begin(); it != m->end();) it = (it->second == k) ? m->erase(it) : std::next(it);
     }
+    for (int i = 1; i < b200_key::kMaxLanes; ++i)
+        if (k->lanes[i]) { b200_key_free(k->lanes[i]); k->lanes[i] = nullptr; }
     DeviceGuard dev_guard(k->dk.device);
     cudaDeviceSynchronize();            // calls enqueued on caller streams may still be using the workspaces
-    if (k->dk.bkfft) cudaFree(k->dk.bkfft);
-    if (k->dk.ks) cudaFree(k->dk.ks);
+    if (k->owns_blobs && k->dk.bkfft) cudaFree(k->dk.bkfft);
+    if (k->owns_blobs && k->dk.ks) cudaFree(k->dk.ks);
     for (DevBuf *b : {&k->u, &k->in0, &k->in1, &k->in2, &k->out, &k->nz, &k->desc_rot, &k->desc_ks, &k->desc_lin, &k->desc_io, &k->acc}) b->release();
     k->stage_in.release();
     k->stage_out.release();
@@ -431,7 +455,8 @@ extern "C" int b200_gate_batch_dev(b200_key *k, int op, int32_t *d_out, const in
     if (count < 0) return fail("negative count");
     if (count == 0) return 0;
     if (!d_out) return fail("d_out is NULL");
-    std::lock_guard<std::mutex> g(k->mu);
+    LaneGuard lane(k);
+    k = lane.k;
     B200_ON_DEVICE(k->dk.device);
     k->timing_pending = true;
     return enqueue_gates(k, op, d_out, d_a, d_b, d_c, count, nullptr, (cudaStream_t)stream, true);
@@ -535,8 +560,8 @@ extern "C" int b200_gate_batch_host(b200_key *k, int op, int32_t *out, const int
     if (!op_valid(op)) return fail("invalid gate op");
     if (count < 0) return fail("negative count");
     if (count == 0) return 0;
-    std::lock_guard<std::mutex> g(k->mu);
-    return gate_batch_host_locked(k, op, out, a, b, c, count, nullptr);
+    LaneGuard lane(k);
+    return gate_batch_host_locked(lane.k, op, out, a, b, c, count, nullptr);
 }
 
 extern "C" int b200_last_timing_ms(b200_key *k, float out_ms[3]) {
@@ -557,12 +582,8 @@ extern "C" int b200_last_timing_ms(b200_key *k, float out_ms[3]) {
     return 0;
 }
 
-extern "C" int b200_timing_drain(b200_key *k, double sum_ms[2], int32_t *calls) {
-    if (!k || !sum_ms || !calls) return fail("NULL argument");
+static int timing_drain_one(b200_key *k, double sum_ms[2], int32_t *calls) {
     std::lock_guard<std::mutex> g(k->mu);
-    B200_ON_DEVICE(k->dk.device);
-    sum_ms[0] = sum_ms[1] = 0;
-    *calls = 0;
     const int64_t begin = std::max(k->ring_drained, k->ring_head - b200_key::kRing);
     for (int64_t c = begin; c < k->ring_head; ++c) {
         cudaEvent_t *ev = k->ring[c % b200_key::kRing];
@@ -575,6 +596,22 @@ extern "C" int b200_timing_drain(b200_key *k, double sum_ms[2], int32_t *calls) 
         ++*calls;
     }
     k->ring_drained = k->ring_head;
+    return 0;
+}
+extern "C" int b200_timing_drain(b200_key *k, double sum_ms[2], int32_t *calls) {
+    if (!k || !sum_ms || !calls) return fail("NULL argument");
+    B200_ON_DEVICE(k->dk.device);
+    sum_ms[0] = sum_ms[1] = 0;
+    *calls = 0;
+    if (timing_drain_one(k, sum_ms, calls)) return 1;
+    for (int i = 1; i < b200_key::kMaxLanes; ++i) {     // calls that ran on a lane while the key was busy
+        b200_key *l;
+        {
+            std::lock_guard<std::mutex> g(k->lanes_mu);
+            l = k->lanes[i];
+        }
+        if (l && timing_drain_one(l, sum_ms, calls)) return 1;
+    }
     return 0;
 }
 
@@ -772,7 +809,9 @@ static int gate_batch_samples(b200_key *k, int op, LweSample *const *out, const 
     const bool need_a = !(op == B200_CONST0 || op == B200_CONST1);
     const bool need_b = !op_is_linear(op), need_c = op == B200_MUX;
     if (!out || (need_a && !a) || (need_b && !b) || (need_c && !c)) return fail("NULL sample array");
-    std::lock_guard<std::mutex> g(k->mu);
+    b200_key *const master = k;
+    LaneGuard lane(k);
+    k = lane.k;
     const size_t row = (size_t)n1 * sizeof(int32_t), bytes = row * count;
     if (k->stage_in.ensure(3 * bytes) || k->stage_out.ensure(bytes + (size_t)count * sizeof(int32_t))) return 1;
     int32_t *ha = (int32_t *)k->stage_in.p, *hb = ha + (size_t)count * n1, *hc = hb + (size_t)count * n1;
@@ -787,7 +826,7 @@ static int gate_batch_samples(b200_key *k, int op, LweSample *const *out, const 
     if (need_a) gather(ha, a);
     if (need_b) gather(hb, b);
     if (need_c) gather(hc, c);
-    if (b200_multi *m = multi_for_key(k)) {
+    if (b200_multi *m = (k == master ? multi_for_key(master) : nullptr)) {   // replicas hang off the key itself, not its lanes
         // B200TFHE_DEVICES: the staged batch is cut over the replicas (this key's mutex is held: the replicas'
         // mutexes are taken by their own threads, device 0's slice by re-entering with the lock already ours)
         if (multi_gate_batch_locked0(m, op, ho, ha, hb, hc, count, hnz)) return 1;
@@ -896,8 +935,8 @@ extern "C" int b200_bootstrap_woks_host(b200_key *k, int32_t *u, const int32_t *
     if (count < 0 || count > kChunkItems) return fail("count out of range");
     if (count == 0) return 0;
     if (!u || !x) return fail("NULL batch pointer");
-    std::lock_guard<std::mutex> g(k->mu);
-    return woks_locked(k, u, x, mu, count);
+    LaneGuard lane(k);
+    return woks_locked(lane.k, u, x, mu, count);
 }
 
 extern "C" int b200_keyswitch_dev(b200_key *k, int32_t *d_out, const int32_t *d_u, int64_t count, void *stream) {
@@ -905,7 +944,8 @@ extern "C" int b200_keyswitch_dev(b200_key *k, int32_t *d_out, const int32_t *d_
     if (count < 0) return fail("negative count");
     if (count == 0) return 0;
     if (!d_out || !d_u) return fail("NULL device pointer");
-    std::lock_guard<std::mutex> g(k->mu);
+    LaneGuard lane(k);
+    k = lane.k;
     B200_ON_DEVICE(k->dk.device);
     KeySwitchArgs ks{};
     ks.u = d_u;
@@ -940,8 +980,8 @@ extern "C" int b200_keyswitch_host(b200_key *k, int32_t *out, const int32_t *u, 
     if (count < 0 || count > kChunkItems) return fail("count out of range");
     if (count == 0) return 0;
     if (!out || !u) return fail("NULL batch pointer");
-    std::lock_guard<std::mutex> g(k->mu);
-    return keyswitch_locked(k, out, u, nonzero, count);
+    LaneGuard lane(k);
+    return keyswitch_locked(lane.k, out, u, nonzero, count);
 }
 
 static int cmux_host(b200_key *k, int32_t *acc, int32_t bk_index, int32_t barai, int mode, int64_t count) {
@@ -951,7 +991,8 @@ static int cmux_host(b200_key *k, int32_t *acc, int32_t bk_index, int32_t barai,
     if (!acc) return fail("acc is NULL");
     if (bk_index < 0 || bk_index >= k->dk.n) return fail("bk_index out of range");
     if (barai < 0 || barai >= 2 * k->dk.N) return fail("barai out of range");
-    std::lock_guard<std::mutex> g(k->mu);
+    LaneGuard lane(k);
+    k = lane.k;
     const DeviceKey &d = k->dk;
     cudaStream_t s = k->stream;
     B200_ON_DEVICE(d.device);
@@ -1009,8 +1050,8 @@ extern "C" void tfhe_bootstrap_woKS_FFT(LweSample *result, const LweBootstrappin
     std::memcpy(xin.data(), x->a, n * 4);
     xin[n] = x->b;
     {
-        std::lock_guard<std::mutex> g(k->mu);
-        if (woks_locked(k, u.data(), xin.data(), mu, 1)) die("tfhe_bootstrap_woKS_FFT");
+        LaneGuard lane(k);
+        if (woks_locked(lane.k, u.data(), xin.data(), mu, 1)) die("tfhe_bootstrap_woKS_FFT");
     }
     std::memcpy(result->a, u.data(), N * 4);
     result->b = u[N];
@@ -1025,8 +1066,8 @@ extern "C" void lweKeySwitch(LweSample *result, const LweKeySwitchKey *ks, const
     std::memcpy(u.data(), sample->a, N * 4);
     u[N] = sample->b;
     {
-        std::lock_guard<std::mutex> g(k->mu);
-        if (keyswitch_locked(k, out.data(), u.data(), &nz, 1)) die("lweKeySwitch");
+        LaneGuard lane(k);
+        if (keyswitch_locked(lane.k, out.data(), u.data(), &nz, 1)) die("lweKeySwitch");
     }
     std::memcpy(result->a, out.data(), n * 4);
     result->b = out[n];
@@ -1041,9 +1082,9 @@ extern "C" void tfhe_bootstrap_FFT(LweSample *result, const LweBootstrappingKeyF
     std::memcpy(xin.data(), x->a, n * 4);
     xin[n] = x->b;
     {
-        std::lock_guard<std::mutex> g(k->mu);
-        if (woks_locked(k, u.data(), xin.data(), mu, 1)) die("tfhe_bootstrap_FFT");
-        if (keyswitch_locked(k, out.data(), u.data(), &nz, 1)) die("tfhe_bootstrap_FFT");
+        LaneGuard lane(k);
+        if (woks_locked(lane.k, u.data(), xin.data(), mu, 1)) die("tfhe_bootstrap_FFT");
+        if (keyswitch_locked(lane.k, out.data(), u.data(), &nz, 1)) die("tfhe_bootstrap_FFT");
     }
     std::memcpy(result->a, out.data(), n * 4);
     result->b = out[n];

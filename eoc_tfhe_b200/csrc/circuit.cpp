@@ -126,7 +126,8 @@ extern "C" int b200_level_run_dev(b200_key *key, int32_t *d_wires, const int32_t
                                   const int32_t *ks_desc, int64_t n_ks, void *stream) {
     if (!key || !key->filled) return b200_fail("key is NULL or not filled");
     if (!d_wires || !rot_desc || !ks_desc) return b200_fail("NULL argument");
-    std::lock_guard<std::mutex> g(key->mu);
+    LaneGuard lane(key);
+    key = lane.k;
     B200_ON_DEVICE(key->dk.device);
     return level_run_locked(key, d_wires, rot_desc, n_rot, ks_desc, n_ks, (cudaStream_t)stream);
 }
@@ -206,7 +207,8 @@ extern "C" int b200_circuit_run_dev(b200_key *key, const int32_t *gates, int64_t
     return b200_guarded([&]() -> int {
         if (!key || !key->filled) return b200_fail("key is NULL or not filled");
         if (!gates || !d_wires) return b200_fail("NULL argument");
-        std::lock_guard<std::mutex> g(key->mu);
+        LaneGuard lane(key);
+    key = lane.k;
         B200_ON_DEVICE(key->dk.device);
         return circuit_run_locked(key, gates, num_gates, d_wires, num_wires, levels_out, (cudaStream_t)stream);
     });
@@ -217,7 +219,8 @@ extern "C" int b200_circuit_run_host(b200_key *key, const int32_t *gates, int64_
     return b200_guarded([&]() -> int {
         if (!key || !key->filled) return b200_fail("key is NULL or not filled");
         if (!gates || !wires) return b200_fail("NULL argument");
-        std::lock_guard<std::mutex> g(key->mu);
+        LaneGuard lane(key);
+    key = lane.k;
         B200_ON_DEVICE(key->dk.device);
         const size_t bytes = (size_t)num_wires * (key->dk.n + 1) * 4;
         if (key->out.ensure(bytes)) return 1;
@@ -254,7 +257,8 @@ extern "C" int b200_circuit_run_host_io(b200_key *key, const int32_t *gates, int
             int32_t *d = &desc[(size_t)(n_in + i) * 4];
             d[0] = B200_COPY; d[1] = (int32_t)(num_wires + n_in + i); d[2] = out_wires[i]; d[3] = 0;
         }
-        std::lock_guard<std::mutex> g(key->mu);
+        LaneGuard lane(key);
+    key = lane.k;
         B200_ON_DEVICE(key->dk.device);
         const size_t row = (size_t)(key->dk.n + 1) * 4;
         if (key->out.ensure((size_t)(num_wires + n_in + n_out) * row)) return 1;

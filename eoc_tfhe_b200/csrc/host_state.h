@@ -3,7 +3,9 @@
 #include "engine.cuh"
 
 #include <exception>
+#include <functional>
 #include <mutex>
+#include <thread>
 #include <new>
 #include <string>
 
@@ -119,6 +121,15 @@ struct b200_key {
         return 0;
     }
     uint64_t fingerprint = 0;           // of the libtfhe cloud key this device key was uploaded from (cache validation)
+    // Lanes: up to kMaxLanes - 1 shallow replicas of this key on the SAME device -- the same resident blobs, their
+    // own streams, workspaces, staging buffers and mutex -- created when a call finds the key busy, so that calls
+    // from several host threads (one gate stream per thread, as the reference's users run libtfhe) overlap on the
+    // GPU instead of queueing on one mutex.  A lane is never visible to the caller.
+    static constexpr int kMaxLanes = 4;
+    b200_key *lanes[kMaxLanes] = {};    // [0] unused
+    std::mutex lanes_mu;
+    b200_key *master = nullptr;         // set in a lane
+    bool owns_blobs = true;
     PinnedBuf stage_in, stage_out;
     // ring of CUDA-event triplets (before blind rotation, between, after key switch), one per gate call
     static constexpr int kRing = 64;
@@ -127,4 +138,30 @@ struct b200_key {
     cudaEvent_t ev_start = nullptr;     // start of the most recent *_host call (incl. copies)
     float last_ms[3] = {0, 0, 0};
     bool timing_pending = false;
+};
+
+b200_key *b200_lane_create(b200_key *master);   // abi.cpp; nullptr on failure (the caller then waits for a busy lane)
+
+// Picks a free lane of the key (the key itself first), creating one if all existing ones are busy and fewer than
+// kMaxLanes exist; otherwise blocks on this thread's home lane.  Holds the lane's mutex for its lifetime.
+struct LaneGuard {
+    b200_key *k;
+    explicit LaneGuard(b200_key *m) : k(nullptr) {
+        if (m->mu.try_lock()) { k = m; return; }
+        for (int i = 1; i < b200_key::kMaxLanes; ++i) {
+            b200_key *l;
+            {
+                std::lock_guard<std::mutex> g(m->lanes_mu);
+                if (!m->lanes[i]) m->lanes[i] = b200_lane_create(m);
+                l = m->lanes[i];
+            }
+            if (l && l->mu.try_lock()) { k = l; return; }
+        }
+        const size_t h = std::hash<std::thread::id>()(std::this_thread::get_id()) % b200_key::kMaxLanes;
+        k = (h == 0 || !m->lanes[h]) ? m : m->lanes[h];
+        k->mu.lock();
+    }
+    ~LaneGuard() { k->mu.unlock(); }
+    LaneGuard(const LaneGuard &) = delete;
+    LaneGuard &operator=(const LaneGuard &) = delete;
 };

@@ -575,3 +575,37 @@ def test_multi_device_entry_equals_single_device(p80):
             assert np.array_equal(got, want), op
     finally:
         L.b200_multi_free(m)
+
+
+def test_concurrent_host_threads_overlap(p80):
+    """One gate stream per host thread, as libtfhe's users run it (and as the CPU arm of the bench does): calls on
+    one key from several threads run on separate lanes (own streams and workspaces, same resident key) instead of
+    queueing on one mutex.  Results equal the sequential ones word for word; four threads finish well inside the
+    time of four sequential streams."""
+    import time
+    from concurrent.futures import ThreadPoolExecutor
+    from eoc_tfhe_b200 import GateOp
+    rk, ck = p80
+    rng = np.random.default_rng(8)
+    threads, per = 4, 40
+    bits_a, bits_b = rng.integers(0, 2, size=threads * per), rng.integers(0, 2, size=threads * per)
+    a, b = rk.encrypt_bits(bits_a), rk.encrypt_bits(bits_b)
+
+    def stream(tid):          # `per` single-gate calls, like a loop of bootsNAND
+        return [ck.gate(GateOp.NAND, a[i:i + 1], b[i:i + 1]) for i in range(tid * per, (tid + 1) * per)]
+
+    stream(0)                 # warm-up: lanes are created on first contention, kernels loaded
+    t0 = time.perf_counter()
+    seq = [stream(t) for t in range(threads)]
+    t_seq = time.perf_counter() - t0
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        list(ex.map(stream, range(threads)))          # creates the lanes
+        t0 = time.perf_counter()
+        par = list(ex.map(stream, range(threads)))
+        t_par = time.perf_counter() - t0
+    for t in range(threads):
+        for x, y in zip(seq[t], par[t]):
+            assert np.array_equal(x, y)
+    out = np.concatenate([np.concatenate(s) for s in par])
+    assert np.array_equal(rk.decrypt_bits(out), 1 - (bits_a & bits_b))
+    assert t_par < 0.6 * t_seq, (t_par, t_seq)
