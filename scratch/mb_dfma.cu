@@ -58,6 +58,28 @@ __global__ void __launch_bounds__(THREADS, 1) k(int mode, double *sink, long lon
             for (int k2 = 0; k2 < 9; ++k2)
 #pragma unroll
                 for (int r = 0; r < 8; ++r) x[r] = fma(a[(r + k2) & 7], c_k[k2 & 7], x[r]);
+        } else if (mode == 8) {          // 72 DADD, one shared operand
+#pragma unroll
+            for (int k2 = 0; k2 < 9; ++k2)
+#pragma unroll
+                for (int r = 0; r < 8; ++r) x[r] = x[r] + e;
+        } else if (mode == 9) {          // 72 DADD, two distinct register operands
+#pragma unroll
+            for (int k2 = 0; k2 < 9; ++k2)
+#pragma unroll
+                for (int r = 0; r < 8; ++r) x[r] = x[r] + a[(r + k2) & 7];
+        } else if (mode == 10) {         // 72 DMUL
+#pragma unroll
+            for (int k2 = 0; k2 < 9; ++k2)
+#pragma unroll
+                for (int r = 0; r < 8; ++r) x[r] = x[r] * c;
+        } else if (mode == 11) {         // one inverse (GS) radix-2 butterfly network: 12 x (4 DADD + 2 DFMA + 2 DMUL)
+#define GS(u, v, ct) { const double dr = u.x - v.x, di = u.y - v.y; u.x += v.x; u.y += v.y; const double wr = fma(ct.y, di, dr), wi = fma(-ct.y, dr, di); v.x = ct.x * wr; v.y = ct.x * wi; }
+            GS(z[0], z[1], w2) GS(z[2], z[3], w2) GS(z[4], z[5], w2) GS(z[6], z[7], w2)
+            GS(z[0], z[2], w1) GS(z[1], z[3], w1) GS(z[4], z[6], w1) GS(z[5], z[7], w1)
+            GS(z[0], z[4], w0) GS(z[1], z[5], w0) GS(z[2], z[6], w0) GS(z[3], z[7], w0)
+#pragma unroll
+            for (int r = 0; r < 8; ++r) { z[r].x *= 0.125; z[r].y *= 0.125; }
         } else {
             // mode 5: 72 DFMA (as mode 0) + 16 I2F.F64.S32; mode 6: the 16 I2F alone; mode 7: 72 DFMA + 16 DADD conversions
             if (mode != 6) {
@@ -113,7 +135,9 @@ int main() {
     run<T>(2, "72 DFMA x = fma(a_r, c, x)", 72, sink, cyc); run<T>(3, "radix-8 pass: 72 DFMA + 16 DMUL", 88, sink, cyc); \
     run<T>(4, "72 DFMA x = fma(a_r, c[bank], x)", 72, sink, cyc); \
     run<T>(6, "16 I2F.F64.S32 + 16 DADD alone", 32, sink, cyc); run<T>(5, "72 DFMA + 16 I2F.F64.S32 + 16 DADD", 88, sink, cyc); \
-    run<T>(7, "72 DFMA + 16 magic-number conversions + 24 DADD", 112, sink, cyc);
+    run<T>(7, "72 DFMA + 16 magic-number conversions + 24 DADD", 112, sink, cyc); \
+    run<T>(8, "72 DADD x = x + e", 72, sink, cyc); run<T>(9, "72 DADD x = x + a_r", 72, sink, cyc); run<T>(10, "72 DMUL x = x * c", 72, sink, cyc); \
+    run<T>(11, "inverse radix-8 pass: 48 DADD + 24 DFMA + 24+16 DMUL", 112, sink, cyc);
     ALL(128) ALL(256) ALL(384)
     printf("status: %s\n", cudaGetErrorString(cudaGetLastError()));
     return 0;
