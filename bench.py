@@ -231,40 +231,61 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def nccl_log_setup(rank):
-    """NCCL's INFO log goes to a per-rank file (stdout carries exactly one JSON line); rank 0 relays the lines that
-    show the communicator (ranks, transports, NVLS) to stderr after the run."""
-    os.environ.setdefault("NCCL_DEBUG", "INFO")
-    os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT,ENV")
-    path = os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/b200_nccl_%h_%p.log")
-    return path
+class NcclLog:
+    """NCCL's INFO log is left on (the driver reads the communicator size from it) without letting it reach this
+    process's stdout, which carries exactly one JSON line: before torch is imported, file descriptor 1 is pointed at
+    a per-process file (NCCL logs to the C stdout unless NCCL_DEBUG_FILE says otherwise), the JSON line is written to
+    the saved descriptor, and rank 0 relays the lines that show the communicator (ranks, transports, NVLS) to stderr
+    after the process group is gone."""
 
+    def __init__(self):
+        os.environ.setdefault("NCCL_DEBUG", "INFO")
+        os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT,ENV")
+        self.debug_file = os.environ.get("NCCL_DEBUG_FILE")       # respected when the launcher set one
+        sys.stdout.flush()
+        self.real_stdout = os.dup(1)
+        self.path = "/tmp/b200_bench_stdout_%d.log" % os.getpid()
+        fd = os.open(self.path, os.O_WRONLY | os.O_CREAT | os.O_TRUNC, 0o600)
+        os.dup2(fd, 1)
+        os.close(fd)
 
-def nccl_log_relay(path, world):
-    import glob
-    import re
-    pat = path.replace("%h", "*").replace("%p", str(os.getpid()))
-    out = {"nranks": None, "lines": 0, "nvls": False}
-    for f in glob.glob(pat):
-        try:
-            with open(f) as fh:
-                for line in fh:
-                    if re.search(r"nranks|Init COMPLETE|NVLS|Channel 00|via P2P|NCCL version", line):
-                        out["lines"] += 1
-                        if out["lines"] <= 40:
-                            sys.stderr.write(line if line.endswith("\n") else line + "\n")
+    def emit(self, text):
+        os.write(self.real_stdout, (text + "\n").encode())
+
+    def relay(self, world):
+        import ctypes
+        import glob
+        import re
+        sys.stdout.flush()
+        ctypes.CDLL(None).fflush(None)
+        files = [self.path]
+        if self.debug_file:
+            files += glob.glob(self.debug_file.replace("%h", "*").replace("%p", str(os.getpid())))
+        out = {"nranks": None, "lines": 0, "nvls": False}
+        for f in files:
+            try:
+                with open(f, errors="replace") as fh:
+                    for line in fh:
+                        if "NCCL" not in line:
+                            continue
                         m = re.search(r"nranks (\d+)", line)
                         if m:
                             out["nranks"] = int(m.group(1))
                         if "NVLS" in line and "comm" in line:
                             out["nvls"] = True
-        except OSError:
-            pass
-    out["comm_nranks_ok"] = out["nranks"] == world
-    return out
+                        if re.search(r"nranks|Init COMPLETE|NVLS|Channel 00|via P2P|NCCL version", line):
+                            out["lines"] += 1
+                            if out["lines"] <= 40:
+                                sys.stderr.write(line if line.endswith("\n") else line + "\n")
+            except OSError:
+                pass
+        sys.stderr.flush()
+        out["comm_nranks_ok"] = out["nranks"] == world
+        return out
 
 
 def main_b200(args):
+    nccl_log = NcclLog() if int(os.environ.get("WORLD_SIZE", "1")) > 1 else None      # before torch loads NCCL
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -274,7 +295,6 @@ def main_b200(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the GPU path has no CPU fallback; use --impl reference for the CPU arm)")
-    nccl_path = nccl_log_setup(rank) if world > 1 else None
     from eoc_tfhe_b200 import (CloudKey, GateOp, PARAMS_80, PARAMS_128, launch_count, fp64_peak_tflops, int32_add_peak,
                                set_blind_rotate_kernel, shard)
     torch.cuda.set_device(local)
@@ -527,11 +547,13 @@ def main_b200(args):
     ck.close()
     if world > 1:
         dist.barrier()
-        dist.destroy_process_group()      # NCCL flushes its log file when the communicator goes
+        dist.destroy_process_group()
     if rank == 0:
-        if world > 1:
-            line["nccl"] = nccl_log_relay(nccl_path, world)
-        print(json.dumps(line), flush=True)
+        if nccl_log:
+            line["nccl"] = nccl_log.relay(world)
+            nccl_log.emit(json.dumps(line))
+        else:
+            print(json.dumps(line), flush=True)
     return 0
 
 

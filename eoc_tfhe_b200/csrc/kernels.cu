@@ -881,6 +881,7 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
 #include "blind_rotate5.cuh"
 #endif
 #include "blind_rotate_lat.cuh"
+#include "blind_rotate_lat2.cuh"
 namespace b200 {
 
 // FftSmem: several CTAs per SM; FftTm: one CTA per SM owns the tensor memory (512 columns), so the CTA walks a slice
@@ -1290,6 +1291,18 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         if (lat < 0) { const char *e = getenv("B200_LAT"); lat = e ? atoi(e) : 1; }
         if (lat && a.items <= sms && br_variant() == 0) {
             cudaError_t el = cudaErrorInvalidValue;
+            // at most one ciphertext per SM pair: a cluster of two CTAs per ciphertext (B200_LAT=2: never, 3: smem transform)
+            if (lat != 2 && 2 * a.items <= sms) {
+                if (lat == 3) {
+                    if (key.l == 2 && key.Bgbit == 10) el = lat2_launch<2, 10, FftSmem>(key, a, s);
+                } else {
+                    if (key.l == 2 && key.Bgbit == 10) el = lat2_launch<2, 10, FftTm>(key, a, s);
+                    else if (key.l == 3 && key.Bgbit == 7) el = lat2_launch<3, 7, FftTm>(key, a, s);
+                    else if (key.l == 2 && key.Bgbit == 8) el = lat2_launch<2, 8, FftTm>(key, a, s);
+                }
+                if (el == cudaSuccess) { COUNT_LAUNCH(); return cudaGetLastError(); }
+                if (el != cudaErrorInvalidValue) return el;
+            }
             if (key.l == 2 && key.Bgbit == 10) el = lat_launch<2, 10>(key, a, s);
             else if (key.l == 3 && key.Bgbit == 7) el = lat_launch<3, 7>(key, a, s);
             else if (key.l == 2 && key.Bgbit == 8) el = lat_launch<2, 8>(key, a, s);
@@ -1537,8 +1550,25 @@ cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaS
         const int64_t per_cta = small ? 64 : 40;
         const bool full = a.items >= sms * per_cta;
         if (ks_sel == 2 || a.items >= sms * 20) {
-            cudaError_t e = small ? (full ? ks2_launch<64, 8, 8, 2>(key, a, s) : ks2_launch<64, 4, 8, 2>(key, a, s))
-                                  : (full ? ks2_launch<96, 5, 8, 2>(key, a, s) : ks2_launch<96, 3, 8, 2>(key, a, s));
+            // Row choice (B200_KS_MODE, A/B only): 0 = uniform 3-way branch per sample and digit (default);
+            // 1 / 2 = one 16-way switch per sample pair / digit pair (nvcc lowers it to a compare tree);
+            // 3 / 4 = the same through one brx.idx jump table each.  All bit-identical; 65,536 samples take
+            // 25.7 / 29.7 / 27.9 / 25.6 / 25.3 ms: fewer instructions do not help, the bound is the latency of
+            // the decisions one warp makes in sequence.
+            static const int ks_mode = [] { const char *m = getenv("B200_KS_MODE"); return m ? atoi(m) : 0; }();
+            cudaError_t e;
+            if (small && full && stride4 == 126) {        // 80-bit set: row stride known at compile time
+                e = ks_mode == 1 ? ks2_launch<64, 8, 8, 2, 1, 126>(key, a, s)
+                  : ks_mode == 2 ? ks2_launch<64, 8, 8, 2, 2, 126>(key, a, s)
+                  : ks_mode == 3 ? ks2_launch<64, 8, 8, 2, 3, 126>(key, a, s)
+                  : ks_mode == 4 ? ks2_launch<64, 8, 8, 2, 4, 126>(key, a, s)
+                                 : ks2_launch<64, 8, 8, 2, 0, 126>(key, a, s);
+            } else if (small)
+                e = full ? ks2_launch<64, 8, 8, 2>(key, a, s) : ks2_launch<64, 4, 8, 2>(key, a, s);
+            else if (stride4 == 158)                      // 128-bit set
+                e = full ? ks2_launch<96, 5, 8, 2, 0, 158>(key, a, s) : ks2_launch<96, 3, 8, 2, 0, 158>(key, a, s);
+            else
+                e = full ? ks2_launch<96, 5, 8, 2>(key, a, s) : ks2_launch<96, 3, 8, 2>(key, a, s);
             if (e != cudaSuccess) return e;
             COUNT_LAUNCH();
             return cudaGetLastError();
@@ -1626,21 +1656,20 @@ cudaError_t measure_fp64_peak(double *tflops) {
 }
 
 // int32 add issue peak (roofline denominator of the key switch, which is a stream of 32-bit subtractions):
-// 16 independent chains per thread, x -= y with y changing per iteration so that nothing folds.
+// 16 accumulators per thread, each subtraction taking another accumulator as its operand so that nothing folds
+// (the first version subtracted a loop-invariant value four times and the compiler turned that into one IMAD).
 __global__ void __launch_bounds__(256) k_int_add_peak(int32_t *sink, int iters, int32_t seed) {
     int32_t a[16];
 #pragma unroll
     for (int r = 0; r < 16; ++r) a[r] = seed + threadIdx.x * 17 + r;
-    int32_t y = seed ^ 0x5bd1e995, z = seed + 12345;
 #pragma unroll 1
     for (int i = 0; i < iters; ++i) {
+        // every subtrahend is another accumulator, so no two subtractions can be folded into one multiply-add
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
 #pragma unroll
-            for (int r = 0; r < 16; r += 2) { a[r] -= y; a[r + 1] -= z; }
+            for (int r = 0; r < 16; ++r) a[r] -= a[(r + 5) & 15];
         }
-        y += z;    // two more adds per 64: not counted
-        z ^= i;
     }
     int32_t r = 0;
 #pragma unroll

@@ -38,13 +38,42 @@ __host__ __device__ constexpr int ks2_smem_bytes(int S, int stride) {
 
 __device__ __forceinline__ void ks2_sub(int4 &a, const int4 &v) { a.x -= v.x; a.y -= v.y; a.z -= v.z; a.w -= v.w; }
 
-// TG threads per group (each owns NC int4 column groups), NG groups per CTA, SG samples per group
-template <int TG, int NG, int SG, int NC>
+// One decision for two samples at the same digit position (MODE 1): A, B = their digits.
+template <int A, int B, int NC>
+__device__ __forceinline__ void ks2_two_samples(int4 (&x)[NC], int4 (&y)[NC], const int4 (&r)[3][NC]) {
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+        if (A) ks2_sub(x[c], r[A ? A - 1 : 0][c]);
+        if (B) ks2_sub(y[c], r[B ? B - 1 : 0][c]);
+    }
+}
+// One decision for two adjacent digits of one sample (MODE 2): both rows leave in one three-input add.
+template <int A, int B, int NC>
+__device__ __forceinline__ void ks2_two_digits(int4 (&x)[NC], const int4 (&ra)[3][NC], const int4 (&rb)[3][NC]) {
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+        if (A && B) {
+            const int4 &u = ra[A ? A - 1 : 0][c], &v = rb[B ? B - 1 : 0][c];
+            x[c].x = x[c].x - u.x - v.x; x[c].y = x[c].y - u.y - v.y; x[c].z = x[c].z - u.z - v.z; x[c].w = x[c].w - u.w - v.w;
+        } else if (A) ks2_sub(x[c], ra[A ? A - 1 : 0][c]);
+        else if (B) ks2_sub(x[c], rb[B ? B - 1 : 0][c]);
+    }
+}
+#include "keyswitch_brx.inc"
+#define KS2_CASES16(F)                                                                                     \
+    F(0, 1) F(0, 2) F(0, 3) F(1, 0) F(1, 1) F(1, 2) F(1, 3) F(2, 0) F(2, 1) F(2, 2) F(2, 3) F(3, 0) F(3, 1) \
+    F(3, 2) F(3, 3)
+
+// TG threads per group (each owns NC int4 column groups), NG groups per CTA, SG samples per group.
+// MODE 0: per sample and digit a uniform 3-way branch; 1: one 16-way switch per sample pair; 2: one 16-way switch
+// per digit pair; 3, 4: the same two with the choice made by one indexed jump (brx.idx, keyswitch_brx.inc).  STRIDE4 > 0: the row stride in int4 is a compile-time constant (immediate LDS offsets).
+template <int TG, int NG, int SG, int NC, int MODE = 0, int STRIDE4 = 0>
 __global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keyswitch_tma(const DeviceKey key, const KeySwitchArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     static_assert(SG == 8 || SG == 16, "8 or 16 samples per group");
     constexpr int T = 8, S = NG * SG, WARPS = TG * NG / 32;
-    const int Nin = key.N * key.k, n1 = key.n + 1, stride = key.ks_stride, stride4 = stride >> 2;
+    const int Nin = key.N * key.k, n1 = key.n + 1;
+    const int stride = STRIDE4 > 0 ? STRIDE4 * 4 : key.ks_stride, stride4 = stride >> 2;
     const int stage_bytes = kKs2RowsPerStage * stride * 4;
     unsigned char *ring = smem;
     uint16_t *dig = reinterpret_cast<uint16_t *>(smem + kKs2Stages * stage_bytes);     // [2][chunk][S]
@@ -147,20 +176,66 @@ __global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keys
                 const int q = (chunk * kKs2Chunk + ii) * 2 + jh, s = q % kKs2Stages;
                 mbar_wait(&st->full[s], (uint32_t)(q / kKs2Stages) & 1u);
                 const int4 *rows = reinterpret_cast<const int4 *>(ring + (size_t)s * stage_bytes);
+                if (MODE == 0) {
 #pragma unroll
-                for (int jj = 0; jj < 4; ++jj) {
-                    int4 r[3][NC];
+                    for (int jj = 0; jj < 4; ++jj) {
+                        int4 r[3][NC];
 #pragma unroll
-                    for (int h = 0; h < 3; ++h)
+                        for (int h = 0; h < 3; ++h)
 #pragma unroll
-                        for (int c = 0; c < NC; ++c) r[h][c] = rows[(jj * 3 + h) * stride4 + col[c]];
-                    const int sh = 2 * (T - 1 - (jh * 4 + jj));
+                            for (int c = 0; c < NC; ++c) r[h][c] = rows[(jj * 3 + h) * stride4 + col[c]];
+                        const int sh = 2 * (T - 1 - (jh * 4 + jj));
 #pragma unroll
-                    for (int g = 0; g < SG; ++g) {
-                        const uint32_t d = ((w[g >> 1] >> (16 * (g & 1))) >> sh) & 3u;
-                        if (d == 1) { _Pragma("unroll") for (int c = 0; c < NC; ++c) ks2_sub(acc[g][c], r[0][c]); }
-                        else if (d == 2) { _Pragma("unroll") for (int c = 0; c < NC; ++c) ks2_sub(acc[g][c], r[1][c]); }
-                        else if (d == 3) { _Pragma("unroll") for (int c = 0; c < NC; ++c) ks2_sub(acc[g][c], r[2][c]); }
+                        for (int g = 0; g < SG; ++g) {
+                            const uint32_t d = ((w[g >> 1] >> (16 * (g & 1))) >> sh) & 3u;
+                            if (d == 1) { _Pragma("unroll") for (int c = 0; c < NC; ++c) ks2_sub(acc[g][c], r[0][c]); }
+                            else if (d == 2) { _Pragma("unroll") for (int c = 0; c < NC; ++c) ks2_sub(acc[g][c], r[1][c]); }
+                            else if (d == 3) { _Pragma("unroll") for (int c = 0; c < NC; ++c) ks2_sub(acc[g][c], r[2][c]); }
+                        }
+                    }
+                } else if (MODE == 1 || MODE == 3) {
+#pragma unroll 1
+                    for (int jj = 0; jj < 4; ++jj) {
+                        int4 r[3][NC];
+#pragma unroll
+                        for (int h = 0; h < 3; ++h)
+#pragma unroll
+                            for (int c = 0; c < NC; ++c) r[h][c] = rows[(jj * 3 + h) * stride4 + col[c]];
+                        const int sh = 2 * (T - 1 - (jh * 4 + jj));
+#pragma unroll
+                        for (int p = 0; p < SG / 2; ++p) {
+                            const uint32_t wp = w[p] >> sh;           // sample 2p in bits 0-1, sample 2p+1 in bits 16-17
+                            if constexpr (MODE == 3 && NC == 2) { ks2_brx_two_samples(acc[2 * p], acc[2 * p + 1], r, (wp & 3u) | ((wp >> 14) & 12u)); continue; }
+                            switch ((wp & 3u) | ((wp >> 14) & 12u)) {
+#define KS2_F(B, A) case (A) | ((B) << 2): ks2_two_samples<A, B, NC>(acc[2 * p], acc[2 * p + 1], r); break;
+                                KS2_CASES16(KS2_F)
+#undef KS2_F
+                                default: break;
+                            }
+                        }
+                    }
+                } else {
+#pragma unroll 1
+                    for (int jp = 0; jp < 2; ++jp) {
+                        int4 ra[3][NC], rb[3][NC];
+#pragma unroll
+                        for (int h = 0; h < 3; ++h)
+#pragma unroll
+                            for (int c = 0; c < NC; ++c) {
+                                ra[h][c] = rows[(jp * 6 + h) * stride4 + col[c]];
+                                rb[h][c] = rows[(jp * 6 + 3 + h) * stride4 + col[c]];
+                            }
+                        const int shb = 2 * (T - 1 - (jh * 4 + 2 * jp + 1));   // digit 2jp+1; digit 2jp sits two bits above
+#pragma unroll
+                        for (int g = 0; g < SG; ++g) {
+                            if constexpr (MODE == 4 && NC == 2) { ks2_brx_two_digits(acc[g], ra, rb, (w[g >> 1] >> (16 * (g & 1) + shb)) & 15u); continue; }
+                            switch ((w[g >> 1] >> (16 * (g & 1) + shb)) & 15u) {
+#define KS2_F(A, B) case ((A) << 2) | (B): ks2_two_digits<A, B, NC>(acc[g], ra, rb); break;
+                                KS2_CASES16(KS2_F)
+#undef KS2_F
+                                default: break;
+                            }
+                        }
                     }
                 }
                 // hand the stage back; the last warp of the CTA to do so refills it
@@ -204,20 +279,21 @@ __global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keys
         atomicAdd(a.nonzero + item0 + threadIdx.x, st->nz[threadIdx.x]);
 }
 
-template <int TG, int NG, int SG, int NC>
+template <int TG, int NG, int SG, int NC, int MODE = 0, int STRIDE4 = 0>
 static cudaError_t ks2_launch(const DeviceKey &key, const KeySwitchArgs &a, cudaStream_t s) {
     static bool done[16] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
+    if (STRIDE4 > 0 && key.ks_stride != STRIDE4 * 4) return cudaErrorInvalidValue;
     const int smem = ks2_smem_bytes(NG * SG, key.ks_stride);
     if (smem > 227 * 1024) return cudaErrorInvalidValue;
     if (!(dev < 16 && done[dev])) {
-        cudaError_t e = cudaFuncSetAttribute(k_keyswitch_tma<TG, NG, SG, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(k_keyswitch_tma<TG, NG, SG, NC, MODE, STRIDE4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
         if (dev < 16) done[dev] = true;
     }
     const unsigned grid = (unsigned)((a.items + NG * SG - 1) / (NG * SG));
-    k_keyswitch_tma<TG, NG, SG, NC><<<grid, TG * NG, smem, s>>>(key, a);
+    k_keyswitch_tma<TG, NG, SG, NC, MODE, STRIDE4><<<grid, TG * NG, smem, s>>>(key, a);
     return cudaSuccess;
 }
 
