@@ -14,8 +14,11 @@
 //   * group 0 adds its own l partials and the received one, runs ONE inverse transform and updates ACC[q], which only
 //     this CTA reads in the next step.
 // Per step and SM: l forward transforms side by side, one inverse, two CTA barriers, one mbarrier wait.
-// The transform is a policy (negacyclic_fft_tm.cuh): with the tensor-memory exchanges a lone transform takes
-// about 890 clk against 1,050 through shared memory.  Sums are formed in a different order than in cmux_step, but
+// The transform is a policy (negacyclic_fft_tm.cuh); with l transforms per SM the shared-memory pipe is nearly idle
+// and the plain shared-memory exchanges are as fast as the tensor-memory ones (0.896 against 0.918 ms per rotation
+// at n = 500), so FftSmem is the default.  Measured per step at n = 500 (clock64 build, -DB200_LAT2_PROFILE):
+// decomposition 350, forward 1,000, MAC + hand-off 300, peer's partial in flight 500, inverse 900, update 150 clk;
+// one CTA per ciphertext (k_blind_rotate_lat) takes 5,150.  Sums are formed in a different order than in cmux_step, but
 // every external product is an exact integer convolution that FP64 resolves far inside the rounding margin:
 // outputs are identical to k_blind_rotate (tests/test_gpu_workloads.py).
 #pragma once
@@ -26,6 +29,7 @@
 namespace b200 {
 
 constexpr int kLat2PartBytes = kM * 16;      // one partial spectrum: 512 double2
+constexpr int kLat2HandOffBarrier = 8;       // named barrier (1..l are the groups' own)
 
 template <int L, class FFT> __host__ __device__ constexpr int lat2_smem_used() {
     return kN * 4 + 1280 + L * FFT::kBufElemsPerTransform * 16 + 2 * (L - 1) * kLat2PartBytes + 2 * kLat2PartBytes + 64;
@@ -141,19 +145,27 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 * L, 1) k_blind_r
 #ifdef B200_LAT2_PROFILE
     long long prof[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, last_ = clock64();
 #endif
+    // Key row (q, p) of BK_i, both columns, 16 complex values per thread.  The registers are free from the spectral
+    // MAC of one step to that of the next, so the rows of the NEXT step are requested right after the MAC, in time
+    // every group would otherwise spend waiting (for the peer's partial, or for group 0's inverse transform): neither
+    // the L2 latency nor the issue of the 16 loads is on the step's critical path.
+    double2 b_own[8], b_oth[8];
+    auto next_step = [&](int from) { while (from < n && bara[from] == 0) ++from; return from; };   // cluster-uniform
+    auto request_rows = [&](int step) {
+        const double2 *row = bk + ((size_t)step * KPL + (q * L + p)) * 2 * kM + t;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) { b_own[r] = __ldg(row + q * kM + r * 64); b_oth[r] = __ldg(row + peer * kM + r * 64); }
+    };
+    int i = next_step(0);
+    if (i < n) request_rows(i);
 #pragma unroll 1
-    for (int i = 0; i < n; ++i) {
-        const int ai = bara[i];
-        if (ai == 0) continue;                     // cluster-uniform
+    while (i < n) {
+        const int ai = bara[i], inext = next_step(i + 1);
         const uint32_t par = cnt & 1u, phase = (cnt >> 1) & 1u;
         ++cnt;
         if (threadIdx.x == 0)
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&rx_bar[par])), "r"(kLat2PartBytes) : "memory");
-        // key row (q, p) of BK_i: both columns, 16 complex values per thread, in flight during the transform
-        const double2 *row = bk + ((size_t)i * KPL + (q * L + p)) * 2 * kM + t;
-        double2 b_own[8], b_oth[8];
-#pragma unroll
-        for (int r = 0; r < 8; ++r) { b_own[r] = __ldg(row + q * kM + r * 64); b_oth[r] = __ldg(row + peer * kM + r * 64); }
+        LAT2_T(9);
 
         double2 x[8];
 #pragma unroll
@@ -172,39 +184,47 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 * L, 1) k_blind_r
         LAT2_T(0);
         fft.forward(x, buf, bar);
         LAT2_T(1);
+        // the partial for the peer first: it has the longer way.  Groups 0..l-2 hand theirs to group l-1 through
+        // shared memory and a named barrier they only arrive at; group l-1 adds and pushes while the others go on
         double2 m_own[8], m_oth[8];
 #pragma unroll
         for (int r = 0; r < 8; ++r) {
-            m_own[r].x = x[r].x * b_own[r].x;                  m_own[r].y = x[r].x * b_own[r].y;
-            m_own[r].x = fma(-x[r].y, b_own[r].y, m_own[r].x); m_own[r].y = fma(x[r].y, b_own[r].x, m_own[r].y);
             m_oth[r].x = x[r].x * b_oth[r].x;                  m_oth[r].y = x[r].x * b_oth[r].y;
             m_oth[r].x = fma(-x[r].y, b_oth[r].y, m_oth[r].x); m_oth[r].y = fma(x[r].y, b_oth[r].x, m_oth[r].y);
-        }
-        if (p >= 1) {
-#pragma unroll
-            for (int r = 0; r < 8; ++r) s_own[(p - 1) * kM + r * 64 + t] = m_own[r];
         }
         if (p <= L - 2) {
 #pragma unroll
             for (int r = 0; r < 8; ++r) s_oth[p * kM + r * 64 + t] = m_oth[r];
-        }
-        LAT2_T(2);
-        __syncthreads();   // partial spectra written; every group has finished reading ACC
-        LAT2_T(3);
-        if (p == L - 1) {
+            asm volatile("bar.arrive %0, %1;" ::"r"(kLat2HandOffBarrier), "r"(THREADS) : "memory");
+        } else {
+            asm volatile("bar.sync %0, %1;" ::"r"(kLat2HandOffBarrier), "r"(THREADS) : "memory");
 #pragma unroll
             for (int pp = 0; pp < L - 1; ++pp)
 #pragma unroll
                 for (int r = 0; r < 8; ++r) { const double2 v = s_oth[pp * kM + r * 64 + t]; m_oth[r].x += v.x; m_oth[r].y += v.y; }
             // Push into the peer's rx[par].  The peer read rx[par] two steps ago, before its end-of-step CTA
-            // barrier; it then had to receive OUR previous partial, which we sent after our own barrier of that
-            // step, which our group 0 passed only after reading the peer's partial of the step before: so the
-            // peer's readers of rx[par] are done whenever we get here, without a cluster barrier.
+            // barrier; it then had to receive OUR previous partial, which we sent after our hand-off barrier of that
+            // step, which came after our end-of-step barrier of the step before, which our group 0 passed only after
+            // reading the peer's partial of that step: so the peer's readers of rx[par] are done whenever we get
+            // here, without a cluster barrier.
             const uint32_t dst = peer_rx + (par * kM + t) * 16u, mb = peer_bar + par * 8u;
 #pragma unroll
             for (int r = 0; r < 8; ++r) st_async_peer(dst + r * 64 * 16, m_oth[r], mb);
-            LAT2_T(4);
         }
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            m_own[r].x = x[r].x * b_own[r].x;                  m_own[r].y = x[r].x * b_own[r].y;
+            m_own[r].x = fma(-x[r].y, b_own[r].y, m_own[r].x); m_own[r].y = fma(x[r].y, b_own[r].x, m_own[r].y);
+        }
+        if (p >= 1) {
+#pragma unroll
+            for (int r = 0; r < 8; ++r) s_own[(p - 1) * kM + r * 64 + t] = m_own[r];
+        }
+        if (p != L - 1 && inext < n) request_rows(inext);   // group l-1 is awaited at the barrier: it asks after it
+        LAT2_T(2);
+        __syncthreads();   // partial spectra written; every group has finished reading ACC
+        LAT2_T(3);
+        if (p == L - 1 && inext < n) request_rows(inext);
         if (p == 0) {      // output polynomial q
 #pragma unroll
             for (int pp = 0; pp < L - 1; ++pp)
@@ -228,11 +248,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 * L, 1) k_blind_r
         LAT2_T(7);
         __syncthreads();   // accumulator complete; partial buffers free
         LAT2_T(8);
+        i = inext;
     }
 #ifdef B200_LAT2_PROFILE
     if (t == 0 && item == 0)
-        printf("lat2 cta %u group %d, clk per step: decompose %lld forward %lld mac %lld bar1 %lld sum(+send) %lld wait_rx %lld inverse %lld update %lld bar2 %lld  (steps %u)\n",
-               q, p, prof[0] / cnt, prof[1] / cnt, prof[2] / cnt, prof[3] / cnt, prof[4] / cnt, prof[5] / cnt, prof[6] / cnt, prof[7] / cnt, prof[8] / cnt, cnt);
+        printf("lat2 cta %u group %d, clk per step: decompose %lld forward %lld mac %lld bar1 %lld sum(+send) %lld wait_rx %lld inverse %lld update %lld bar2 %lld key-ldg-issue %lld (steps %u)\n",
+               q, p, prof[0] / cnt, prof[1] / cnt, prof[2] / cnt, prof[3] / cnt, prof[4] / cnt, prof[5] / cnt, prof[6] / cnt, prof[7] / cnt, prof[8] / cnt, prof[9] / cnt, cnt);
 #endif
 
     // ---- sample extract at index 0 (lwe.cpp:41-60): a from polynomial 0, b from polynomial 1

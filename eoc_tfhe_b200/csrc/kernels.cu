@@ -1291,14 +1291,17 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         if (lat < 0) { const char *e = getenv("B200_LAT"); lat = e ? atoi(e) : 1; }
         if (lat && a.items <= sms && br_variant() == 0) {
             cudaError_t el = cudaErrorInvalidValue;
-            // at most one ciphertext per SM pair: a cluster of two CTAs per ciphertext (B200_LAT=2: never, 3: smem transform)
+            // at most one ciphertext per SM pair: a cluster of two CTAs per ciphertext (blind_rotate_lat2.cuh).
+            // B200_LAT=2: never; 3: with the tensor-memory transform (A/B: 0.918 ms against 0.896 ms per rotation at
+            // n = 500 -- with two transforms per SM the shared-memory pipe is idle enough for the plain exchanges)
             if (lat != 2 && 2 * a.items <= sms) {
                 if (lat == 3) {
-                    if (key.l == 2 && key.Bgbit == 10) el = lat2_launch<2, 10, FftSmem>(key, a, s);
-                } else {
                     if (key.l == 2 && key.Bgbit == 10) el = lat2_launch<2, 10, FftTm>(key, a, s);
                     else if (key.l == 3 && key.Bgbit == 7) el = lat2_launch<3, 7, FftTm>(key, a, s);
-                    else if (key.l == 2 && key.Bgbit == 8) el = lat2_launch<2, 8, FftTm>(key, a, s);
+                } else {
+                    if (key.l == 2 && key.Bgbit == 10) el = lat2_launch<2, 10, FftSmem>(key, a, s);
+                    else if (key.l == 3 && key.Bgbit == 7) el = lat2_launch<3, 7, FftSmem>(key, a, s);
+                    else if (key.l == 2 && key.Bgbit == 8) el = lat2_launch<2, 8, FftSmem>(key, a, s);
                 }
                 if (el == cudaSuccess) { COUNT_LAUNCH(); return cudaGetLastError(); }
                 if (el != cudaErrorInvalidValue) return el;

@@ -401,7 +401,7 @@ def test_random_gate_stream_with_dependencies(p80):
 
 
 def test_batch_sizes_across_every_kernel_boundary(p80):
-    """Ragged batches: sizes on both sides of every dispatch boundary (latency kernel <= 148, four ciphertexts
+    """Ragged batches: sizes on both sides of every dispatch boundary (cluster latency kernel <= 74 rotations, latency kernel <= 148, four ciphertexts
     per CTA <= 592, six above; balanced grids with q, q+1 ciphertexts per CTA; gather / streaming key switch)
     give, gate for gate, the words of one large batch -- a gate's output depends on its inputs only.  An empty
     batch is a no-op."""
@@ -418,7 +418,7 @@ def test_batch_sizes_across_every_kernel_boundary(p80):
     b = torch.from_numpy(pool[bits_b] + noise[1]).cuda()
     want = ck.gate(GateOp.XOR, a, b)
     assert np.array_equal(rk.decrypt_bits(want.cpu().numpy()), bits_a ^ bits_b)
-    for count in (1, 2, 147, 148, 149, 150, 295, 297, 445, 591, 592, 593, 739, 887, 888, 889, 1037, 148 * 20 - 1, 148 * 20):
+    for count in (1, 2, 73, 74, 75, 147, 148, 149, 150, 295, 297, 445, 591, 592, 593, 739, 887, 888, 889, 1037, 148 * 20 - 1, 148 * 20):
         buf = torch.full((count + 2, rk.n + 1), 0x5A5A5A5A, dtype=torch.int32, device="cuda")   # guard rows
         ck.gate(GateOp.XOR, a[:count], b[:count], out=buf[1:count + 1])
         assert torch.equal(buf[1:count + 1], want[:count]), count
@@ -426,12 +426,32 @@ def test_batch_sizes_across_every_kernel_boundary(p80):
     # MUX: two rotations per gate, so the boundaries sit at half the counts
     c = torch.roll(a, 1, dims=0)
     want_mux = ck.gate(GateOp.MUX, a, b, c)
-    for count in (1, 74, 75, 296, 297, 444, 445, 500, 888, 889, 1000):
+    for count in (1, 37, 38, 74, 75, 296, 297, 444, 445, 500, 888, 889, 1000):
         got = ck.gate(GateOp.MUX, a[:count], b[:count], c[:count])
         assert torch.equal(got, want_mux[:count]), ("MUX", count)
     out = torch.full((4, rk.n + 1), 7, dtype=torch.int32, device="cuda")
     ck.gate(GateOp.XOR, a[:0], b[:0], out=out[:0])
     assert int((out != 7).sum()) == 0
+
+
+@pytest.mark.parametrize("which", ["p80", "p128"])
+def test_cluster_latency_kernel_word_identical(which, request):
+    """k_blind_rotate_lat2 (one ciphertext on a cluster of two CTAs, partial spectra exchanged through distributed
+    shared memory) forms its sums in another order than the wide kernels; every external product is an exact integer
+    convolution, so the extracted samples must be the SAME words.  1, 3 and 74 rotations (the largest launch that
+    takes it), rows with runs of zero coefficients (skipped steps: the two CTAs must skip in lockstep) and an
+    all-zero row, at both parameter sets (l = 2: two groups per CTA; l = 3: three)."""
+    rk, ck = request.getfixturevalue(which)
+    rng = np.random.default_rng(4242)
+    x = rng.integers(-2**31, 2**31, size=(600, rk.n + 1), dtype=np.int64).astype(np.int32)
+    x[1] = 0
+    x[2, :300] = 0
+    x[3, 100:] = 0
+    x[5, ::2] = 0
+    want = ck.bootstrap_woks(x)          # 600 rotations: the wide kernel
+    for count in (1, 3, 74):
+        assert np.array_equal(ck.bootstrap_woks(x[:count]), want[:count]), count
+    assert np.array_equal(ck.bootstrap_woks(x[500:574]), want[500:574])
 
 
 def test_noiseless_inputs_equal_reference_word_for_word(p80):
