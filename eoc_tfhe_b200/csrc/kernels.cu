@@ -970,10 +970,14 @@ __global__ void __launch_bounds__(64, UsesTm<FFT>::value ? 1 : 6) k_fft_test(con
 // ------------------------------------------------------------------------------------------------
 constexpr int kKsTile = 8;
 
-template <int T>
+// MASKED (one or two tiles, i.e. the lone bootsNAND): only the rows some sample of the tile selects are loaded -- a
+// lone sample needs a quarter of the 24 rows of a coefficient.  Full tiles need nearly all of them and the predicated
+// loads cost more than they save (592 samples: 0.89 against 0.82 ms), so wider batches load unconditionally.
+template <int T, bool MASKED>
 __global__ void __launch_bounds__(160) k_keyswitch(const DeviceKey key, const KeySwitchArgs a, int i_per_split, int nsplit) {
     extern __shared__ __align__(128) unsigned char smem[];
     uint16_t *dig = reinterpret_cast<uint16_t *>(smem);  // [kKsTile][i_per_split]
+    uint32_t *need = reinterpret_cast<uint32_t *>(smem + (((size_t)kKsTile * i_per_split * 2 + 15) & ~(size_t)15));  // [i_per_split]
     __shared__ int nz[kKsTile];
     __shared__ int32_t bterm[kKsTile];
     __shared__ int32_t outrow[kKsTile];
@@ -1002,6 +1006,8 @@ __global__ void __launch_bounds__(160) k_keyswitch(const DeviceKey key, const Ke
         bterm[g] = b;
         outrow[g] = orow;
     }
+    if (MASKED)
+        for (int ii = threadIdx.x; ii < icnt; ii += blockDim.x) need[ii] = 0;
     __syncthreads();
     // digit pre-pass (lwe-keyswitch-functions.cpp:122-125): top 2T bits of a_i + prec_offset
     for (int idx = threadIdx.x; idx < kKsTile * icnt; idx += blockDim.x) {
@@ -1018,6 +1024,15 @@ __global__ void __launch_bounds__(160) k_keyswitch(const DeviceKey key, const Ke
             packed = (v + prec_offset) >> (32 - 2 * T);
             const int c = __popc((packed | (packed >> 1)) & 0x5555u);
             if (c && a.nonzero) atomicAdd(&nz[g], c);
+            if (MASKED) {   // rows of this coefficient that some sample of the tile selects: bit 3 j + (d - 1)
+                uint32_t m = 0;
+#pragma unroll
+                for (int j = 0; j < T; ++j) {
+                    const uint32_t d = (packed >> (2 * (T - 1 - j))) & 3u;
+                    if (d) m |= 1u << (3 * j + d - 1);
+                }
+                if (m) atomicOr(&need[ii], m);
+            }
         }
         dig[g * i_per_split + ii] = (uint16_t)packed;
     }
@@ -1033,10 +1048,12 @@ __global__ void __launch_bounds__(160) k_keyswitch(const DeviceKey key, const Ke
 #pragma unroll 1
         for (int ii = 0; ii < icnt; ++ii) {
             int4 r[T][3];
+            const uint32_t nm = MASKED ? need[ii] : 0xffffffu;   // CTA-uniform
 #pragma unroll
             for (int j = 0; j < T; ++j)
 #pragma unroll
-                for (int h = 0; h < 3; ++h) r[j][h] = __ldg(tab + (size_t)((ii * T + j) * 3 + h) * stride4);
+                for (int h = 0; h < 3; ++h)
+                    if (nm & (1u << (3 * j + h))) r[j][h] = __ldg(tab + (size_t)((ii * T + j) * 3 + h) * stride4);
 #pragma unroll
             for (int g = 0; g < kKsTile; ++g) {
                 const uint32_t pk = dig[g * i_per_split + ii];
@@ -1580,7 +1597,7 @@ cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaS
     const int64_t tiles = (a.items + kKsTile - 1) / kKsTile;
     // enough CTAs to fill 148 SMs several times over; small batches split the i range instead
     int nsplit = 1;
-    while (tiles * nsplit < sms * 4 && nsplit < 64) nsplit *= 2;
+    while (tiles * nsplit < sms * 4 && nsplit < (tiles <= 2 ? 256 : 64)) nsplit *= 2;   // a lone gate: 4 coefficients per CTA
     const int i_per_split = (Nin + nsplit - 1) / nsplit;
     const int threads = ((key.ks_stride / 4) + 31) / 32 * 32;
     if (threads > 160) return cudaErrorInvalidValue;
@@ -1588,9 +1605,10 @@ cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaS
         k_zero_rows<<<(unsigned)a.items, 128, 0, s>>>(a.out, a.desc, a.items, key.n + 1);
         COUNT_LAUNCH();
     }
-    const size_t smem = (size_t)kKsTile * i_per_split * sizeof(uint16_t);
+    const size_t smem = (((size_t)kKsTile * i_per_split * sizeof(uint16_t) + 15) & ~(size_t)15) + (size_t)i_per_split * sizeof(uint32_t);
     dim3 grid((unsigned)tiles, nsplit);
-    k_keyswitch<8><<<grid, threads, smem, s>>>(key, a, i_per_split, nsplit);
+    if (tiles <= 2) k_keyswitch<8, true><<<grid, threads, smem, s>>>(key, a, i_per_split, nsplit);
+    else k_keyswitch<8, false><<<grid, threads, smem, s>>>(key, a, i_per_split, nsplit);
     COUNT_LAUNCH();
     return cudaGetLastError();
 }

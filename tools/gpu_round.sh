@@ -29,3 +29,10 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_b
     -f -o $OUT/${TAG}_prof python scratch/prof_one.py 8880 > $OUT/${TAG}_ncu2.log 2>&1
 tail -3 $OUT/${TAG}_ncu2.log
 ls -la $OUT | tail -12
+# small batches, secondary workloads (BASELINE configs[2], [3]) and one full capture of the cluster latency kernel
+timeout 300 python scratch/small_batches.py > $OUT/${TAG}_small_batches.txt 2>&1
+timeout 1200 python tools/workloads.py all > $OUT/${TAG}_workloads.jsonl 2> $OUT/${TAG}_workloads.err
+timeout 300 python scratch/prof_one.py 1 > $OUT/${TAG}_lat2_plain.log 2>&1 &&
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:'k_blind_rotate_lat2' -s 1 -c 1 \
+    -f -o $OUT/${TAG}_lat2 python scratch/prof_one.py 1 > $OUT/${TAG}_ncu4.log 2>&1
+tail -2 $OUT/${TAG}_ncu4.log
