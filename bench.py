@@ -239,7 +239,8 @@ class NcclLog:
     after the process group is gone."""
 
     def __init__(self):
-        os.environ.setdefault("NCCL_DEBUG", "INFO")
+        if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
+            os.environ["NCCL_DEBUG"] = "INFO"          # a preset VERSION / WARN level hides the communicator lines
         os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT,ENV")
         self.debug_file = os.environ.get("NCCL_DEBUG_FILE")       # respected when the launcher set one
         sys.stdout.flush()
