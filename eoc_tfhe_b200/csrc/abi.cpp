@@ -462,6 +462,43 @@ extern "C" int b200_gate_batch_dev(b200_key *k, int op, int32_t *d_out, const in
     return enqueue_gates(k, op, d_out, d_a, d_b, d_c, count, nullptr, (cudaStream_t)stream, true);
 }
 
+// Same gates as b200_gate_batch_dev with no allocation anywhere on the call: the extracted samples go through the
+// static device array of kernels.cu (launch_gates_noalloc), the key's own mutex serialises the enqueue (no lane is
+// created: that would allocate), and no timing events are recorded.
+extern "C" int b200_gate_batch_dev_noalloc(b200_key *k, int op, int32_t *d_out, const int32_t *d_a, const int32_t *d_b,
+                                           const int32_t *d_c, int64_t count, void *stream) {
+    if (!k || !k->filled) return fail("key is NULL or not filled");
+    if (!op_valid(op)) return fail("invalid gate op");
+    if (count < 0) return fail("negative count");
+    if (count == 0) return 0;
+    if (!d_out) return fail("d_out is NULL");
+    const DeviceKey &d = k->dk;
+    static_assert(kNoAllocMaxRotations == B200_NOALLOC_MAX_ROTATIONS, "header and kernels.cu disagree on the scratch size");
+    const int per = op == B200_MUX ? 2 : 1;
+    if (!op_is_linear(op) && count * per > kNoAllocMaxRotations) {
+        char msg[256];
+        snprintf(msg, sizeof msg, "b200_gate_batch_dev_noalloc: %lld gates need %lld blind rotations, the static scratch holds %lld "
+                 "(B200_NOALLOC_MAX_ROTATIONS); use b200_gate_batch_dev or split the batch",
+                 (long long)count, (long long)(count * per), (long long)kNoAllocMaxRotations);
+        return fail(msg);
+    }
+    std::lock_guard<std::mutex> g(k->mu);
+    B200_ON_DEVICE(d.device);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (op_is_linear(op)) {          // no scratch involved
+        const int sign = op == B200_NOT ? -1 : 1;
+        const int32_t cst = op == B200_CONST1 ? (1 << 29) : (op == B200_CONST0 ? -(1 << 29) : 0);
+        const int32_t *in = (op == B200_NOT || op == B200_COPY) ? d_a : nullptr;
+        if ((op == B200_NOT || op == B200_COPY) && !d_a) return fail("input a is NULL");
+        CK(launch_linear(d, d_out, in, sign, cst, count, s));
+        return 0;
+    }
+    if (!d_a || !d_b || (op == B200_MUX && !d_c)) return fail("gate input pointer is NULL");
+    if (d.N * d.k != 1024) return fail("b200_gate_batch_dev_noalloc: the static scratch is laid out for N * k = 1024");
+    CK(launch_gates_noalloc(d, op, d_out, d_a, d_b, d_c, count, s));
+    return 0;
+}
+
 static int gate_batch_host_locked(b200_key *k, int op, int32_t *out, const int32_t *a, const int32_t *b, const int32_t *c,
                                   int64_t count, int32_t *nonzero) {
     const DeviceKey &d = k->dk;

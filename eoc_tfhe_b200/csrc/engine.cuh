@@ -63,6 +63,11 @@ cudaError_t launch_bk_convert(const DeviceKey &key, const int32_t *d_bk_coefs, c
 cudaError_t launch_ks_pack(const DeviceKey &key, const int32_t *d_ks_rows, cudaStream_t s);
 cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, cudaStream_t s);
 cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaStream_t s);
+// blind rotation + key switch of one gate batch with the extracted samples in a static device array (kernels.cu);
+// at most kNoAllocMaxRotations rotations (MUX: two per gate); the key's device must be current
+constexpr int64_t kNoAllocMaxRotations = 4096;
+cudaError_t launch_gates_noalloc(const DeviceKey &key, int op, int32_t *d_out, const int32_t *d_a, const int32_t *d_b,
+                                 const int32_t *d_c, int64_t count, cudaStream_t s);
 // mode 0: acc <- acc + BK_i (x) ((X^a - 1) acc)   mode 1: acc <- BK_i (x) acc
 cudaError_t launch_cmux_test(const DeviceKey &key, int32_t *d_acc, int bk_index, int barai, int mode,
                              int64_t count, cudaStream_t s);

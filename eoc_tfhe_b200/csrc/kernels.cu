@@ -21,6 +21,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <mutex>
 #include <math.h>
 #include <stdlib.h>
 
@@ -1611,6 +1612,66 @@ cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaS
     else k_keyswitch<8, false><<<grid, threads, smem, s>>>(key, a, i_per_split, nsplit);
     COUNT_LAUNCH();
     return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Gate batch without any allocation (b200_gate_batch_dev_noalloc; no counterpart in the reference, added
+// for callers that cannot call cudaMalloc: graph capture, tight serving loops).
+// The extracted samples that travel from the blind rotation to the key switch -- the workspace b200_gate_batch_dev
+// keeps per key and grows with cudaMalloc -- live in a file-scope device array of fixed size instead: every GPU
+// that loads the library holds kNoAllocMaxRotations x (N + 1) words (16.8 MB) until exit.
+// In host code `g_noalloc_u` is only a stand-in for the symbol, not a device address: the address each device
+// gives it is looked up once per device with cudaGetSymbolAddress (that device current) and passed to the kernels.
+// Every call shares the array and it keeps the previous call's contents.  Nothing in it has to start at zero:
+// the blind rotation writes all N + 1 words of rows 0..rotations-1 before the key switch, later on the same
+// stream, reads exactly those rows.  Calls that overlap on the GPU (different streams, no ordering) race on it.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) int32_t g_noalloc_u[(size_t)kNoAllocMaxRotations * (kN + 1)];
+
+static cudaError_t noalloc_scratch(int device, int32_t **out) {
+    static std::mutex mu;
+    static int32_t *addr[64] = {nullptr};
+    if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> g(mu);
+    if (!addr[device]) {
+        int cur = -1;
+        cudaError_t e = cudaGetDevice(&cur);
+        if (e != cudaSuccess) return e;
+        if (cur != device) return cudaErrorInvalidDevice;     // the symbol resolves on the CURRENT device
+        int32_t *p = nullptr;
+        e = cudaGetSymbolAddress((void **)&p, g_noalloc_u);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        addr[device] = p;
+    }
+    *out = addr[device];
+    return cudaSuccess;
+}
+
+cudaError_t launch_gates_noalloc(const DeviceKey &key, int op, int32_t *d_out, const int32_t *d_a, const int32_t *d_b,
+                                 const int32_t *d_c, int64_t count, cudaStream_t s) {
+    const int per = op == B200_MUX ? 2 : 1;
+    if (count <= 0) return cudaSuccess;
+    if (key.N * key.k != kN || count * per > kNoAllocMaxRotations) return cudaErrorInvalidValue;
+    int32_t *u = nullptr;
+    cudaError_t e = noalloc_scratch(key.device, &u);
+    if (e != cudaSuccess) return e;
+    BlindRotateArgs br{};
+    br.in0 = d_a;
+    br.in1 = d_b;
+    br.in2 = d_c;
+    br.op = op;
+    br.mu = 1 << 29;
+    br.u = u;
+    br.items = count * per;
+    e = launch_blind_rotate(key, br, s);
+    if (e != cudaSuccess) return e;
+    KeySwitchArgs ks{};
+    ks.u = u;
+    ks.pair = per == 2;
+    ks.out = d_out;
+    ks.items = count;
+    return launch_keyswitch(key, ks, s);
 }
 
 cudaError_t launch_linear(const DeviceKey &key, int32_t *d_out, const int32_t *d_in, int sign, int32_t cst,

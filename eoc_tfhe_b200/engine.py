@@ -202,6 +202,24 @@ class CloudKey:
         _lib.check(L.b200_gate_batch_dev(self._h, int(op), _ptr(out), _ptr(a), _ptr(b), _ptr(c), count, C.c_void_p(s)))
         return out
 
+    def gate_noalloc(self, op, a=None, b=None, c=None, out=None, stream=None):
+        """`gate` on device tensors through b200_gate_batch_dev_noalloc: the library allocates nothing on the call
+        (static scratch, at most NOALLOC_MAX_ROTATIONS blind rotations; MUX takes two per gate).  `out` is required:
+        allocating it here would defeat the purpose."""
+        import torch
+        op = GateOp(op)
+        if out is None:
+            raise ValueError("gate_noalloc needs a preallocated `out`")
+        count = out.shape[0]
+        for x in (a, b, c, out):
+            if x is not None and not (x.is_cuda and x.dtype == torch.int32 and x.is_contiguous()
+                                      and tuple(x.shape) == (count, self._rowlen())):
+                raise ValueError("device batches must be contiguous int32 CUDA tensors of shape (count, n+1)")
+        s = stream if stream is not None else torch.cuda.current_stream(out.device).cuda_stream
+        _lib.check(_lib.load().b200_gate_batch_dev_noalloc(self._h, int(op), _ptr(out), _ptr(a), _ptr(b), _ptr(c), count,
+                                                           C.c_void_p(s)))
+        return out
+
     def nand(self, a, b, **kw):
         return self.gate(GateOp.NAND, a, b, **kw)
 

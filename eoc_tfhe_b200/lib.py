@@ -40,6 +40,7 @@ SIGNATURES = {
     "b200_key_device_blobs": (C.c_int, [_VP, C.POINTER(_VP), C.POINTER(C.c_size_t), C.POINTER(_VP), C.POINTER(C.c_size_t)]),
     "b200_gate_batch_host": (C.c_int, [_VP, C.c_int, _VP, _VP, _VP, _VP, C.c_int64]),
     "b200_gate_batch_dev": (C.c_int, [_VP, C.c_int, _VP, _VP, _VP, _VP, C.c_int64, _VP]),
+    "b200_gate_batch_dev_noalloc": (C.c_int, [_VP, C.c_int, _VP, _VP, _VP, _VP, C.c_int64, _VP]),
     "b200_bootstrap_woks_host": (C.c_int, [_VP, _VP, _VP, C.c_int32, C.c_int64]),
     "b200_keyswitch_host": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int64]),
     "b200_keyswitch_dev": (C.c_int, [_VP, _VP, _VP, C.c_int64, _VP]),

@@ -240,6 +240,22 @@ int  b200_gate_batch_host(b200_key *key, int op, int32_t *out, const int32_t *a,
  * a call; a call that is split into chunks (> 2^18 rotations) or pipelined slices reports its first chunk. */
 int  b200_gate_batch_dev(b200_key *key, int op, int32_t *d_out, const int32_t *d_a,
                          const int32_t *d_b, const int32_t *d_c, int64_t count, void *stream);
+/* The same gates, same arguments and same results as b200_gate_batch_dev, for callers that cannot allocate (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The call allocates nothing -- no cudaMalloc / cudaFree, no stream,
+ * event or lane creation: the extracted samples that travel from the blind rotation to the key switch live in a
+ * static device array inside the library, B200_NOALLOC_MAX_ROTATIONS x 1025 words = 16.8 MB, which every GPU that
+ * loads the library holds until exit.
+ * Limit: count (MUX: 2 x count) must not exceed B200_NOALLOC_MAX_ROTATIONS blind rotations; larger batches are
+ * rejected with rc 1 and a b200_last_error() that names the limit.  Keys with N * k != 1024 are rejected.
+ * Sharing: every call on a device uses the same array, whatever the key, and it keeps the previous call's contents
+ * (nothing in it needs to start at zero: each call writes the rows it later reads).  Calls ordered on one stream are
+ * safe; calls that overlap on the GPU (different streams without ordering, several host threads) RACE on the array
+ * and return wrong ciphertexts -- b200_gate_batch_dev has per-key workspaces and no such restriction.
+ * No timing is recorded for these calls (b200_last_timing_ms / b200_timing_drain do not see them). */
+#define B200_NOALLOC_MAX_ROTATIONS 4096
+int  b200_gate_batch_dev_noalloc(b200_key *key, int op, int32_t *d_out, const int32_t *d_a,
+                                 const int32_t *d_b, const int32_t *d_c, int64_t count, void *stream);
 
 /* Several devices behind one handle (north_star: gates partitioned over the GPUs of a box, cloud key replicated).
  * b200_multi_create replicates `key` (which stays owned by the caller and must outlive the handle) onto the listed
