@@ -545,16 +545,14 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
             const int r = 4 * h + i;
             const double2 b0 = rows.load(row + r * 64);
             const double2 b1 = rows.load(row + kM + r * 64);
-            // four products per digit component back to back (kept in this order by volatile asm): the component
-            // stays in the operand reuse cache, so each DFMA reads two fresh registers, not three (a DFMA with three
-            // fresh 64-bit sources issues every 3 clk instead of 2, profiles/r2_microbench_dfma_operands.txt)
-            const double nxy = -x[r].y;
-            asm volatile("fma.rn.f64 %0, %4, %5, %0;\n\tfma.rn.f64 %1, %4, %6, %1;\n\tfma.rn.f64 %2, %4, %7, %2;\n\tfma.rn.f64 %3, %4, %8, %3;"
-                         : "+d"(c0[i].x), "+d"(c0[i].y), "+d"(c1[i].x), "+d"(c1[i].y)
-                         : "d"(x[r].x), "d"(b0.x), "d"(b0.y), "d"(b1.x), "d"(b1.y));
-            asm volatile("fma.rn.f64 %0, %4, %6, %0;\n\tfma.rn.f64 %2, %4, %8, %2;\n\tfma.rn.f64 %1, %5, %7, %1;\n\tfma.rn.f64 %3, %5, %9, %3;"
-                         : "+d"(c0[i].x), "+d"(c0[i].y), "+d"(c1[i].x), "+d"(c1[i].y)
-                         : "d"(nxy), "d"(x[r].y), "d"(b0.y), "d"(b0.x), "d"(b1.y), "d"(b1.x));
+            c0[i].x = fma(x[r].x, b0.x, c0[i].x);
+            c0[i].x = fma(-x[r].y, b0.y, c0[i].x);
+            c0[i].y = fma(x[r].x, b0.y, c0[i].y);
+            c0[i].y = fma(x[r].y, b0.x, c0[i].y);
+            c1[i].x = fma(x[r].x, b1.x, c1[i].x);
+            c1[i].x = fma(-x[r].y, b1.y, c1[i].x);
+            c1[i].y = fma(x[r].x, b1.y, c1[i].y);
+            c1[i].y = fma(x[r].y, b1.x, c1[i].y);
         }
     };
     // MAC event ev over rows rp (and rp + 1 when xb is given): acc (tensor memory, or zero for the first event)
@@ -615,11 +613,7 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
             if (p + 1 < L) {
                 double2 xb[8];
                 digits_pretwisted<BGBIT>(xb, dv, shift - BGBIT);
-#ifdef B200_FWD2_UNSKEWED
-                fft.template forward2u<true>(xa, xb, bufs, bufs + kBuf, bar);
-#else
                 fft.template forward2<true>(xa, xb, bufs, bufs + kBuf, bar);
-#endif
                 mac_event(ev, xa, &xb, q * L + p);
             } else {
                 fft.template forward<true>(xa, bufs, bar);

@@ -367,53 +367,6 @@ struct FftTm {
         fwd_p3b(xb, E0, E1);
     }
 
-    // The same two transforms in LOCKSTEP (no skew): both are at the same butterfly level at the same time, so they
-    // use the same root registers and the scheduler can put a's and b's copies of a butterfly next to each other --
-    // the second then finds the root in the operand reuse cache (a DFMA with three fresh 64-bit register sources
-    // issues every 3 clk, one with two every 2: profiles/r2_microbench_dfma_operands.txt).  The tensor-memory round
-    // trips are then hidden by the other warps of the scheduler instead of by the partner transform.
-    template <bool PRE = false, class Barrier>
-    __device__ __forceinline__ void forward2u(double2 (&xa)[8], double2 (&xb)[8], double2 *bufa, double2 *bufb,
-                                              const Barrier &bar) const {
-        const uint32_t tma = tm, tmb = tm + kTmColExB;
-        if (PRE) { fwd_radix8_first_pretwisted(xa); fwd_radix8_first_pretwisted(xb); }
-        else { fwd_radix8(xa, c_tw.p1); fwd_radix8(xb, c_tw.p1); }
-#pragma unroll
-        for (int r = 0; r < 8; ++r) { bufa[tm_slot(t + 64 * r)] = xa[r]; bufb[tm_slot(t + 64 * r)] = xb[r]; }
-        double rt[8], r3[8];
-        tm_load_roots8(rt, tmr + kTmColRoots2);
-        bar();
-        const int base = tm_slot(rd0);
-#pragma unroll
-        for (int r = 0; r < 8; ++r) { xa[r] = bufa[base + 8 * r]; xb[r] = bufb[base + 8 * r]; }
-        RootSet w2;
-        w2.A = make_double2(rt[0], rt[1]); w2.B = make_double2(rt[2], rt[3]);
-        w2.C = make_double2(rt[4], rt[5]); w2.D = make_double2(rt[6], rt[7]);
-        Tm8 lo, hi;
-        fwd_radix8(xa, w2);
-        fwd_radix8(xb, w2);
-        tm_exchange_fwd_store<1>(xa, tma);
-        tm_exchange_fwd_store<1>(xb, tmb);
-        tm_wait_st();
-        tm_exchange_fwd_load<6>(lo, hi, r3, tma, tma + (16u << 16), tmr + kTmColRoots3a);
-        tm_unpack(xa, lo, hi);
-        tm_exchange_fwd_load<0>(lo, hi, rt, tmb, tmb + (16u << 16), 0);
-        tm_unpack(xb, lo, hi);
-        const double2 A = make_double2(r3[0], r3[1]), C = make_double2(r3[2], r3[3]), D = make_double2(r3[4], r3[5]);
-        fwd_p3a(xa, A, C, D);
-        fwd_p3a(xb, A, C, D);
-        tm_exchange_fwd_store<2>(xa, tma);
-        tm_exchange_fwd_store<2>(xb, tmb);
-        tm_wait_st();
-        tm_exchange_fwd_load<4>(lo, hi, r3, tma, tma + (16u << 16), tmr + kTmColRoots3b);
-        tm_unpack(xa, lo, hi);
-        tm_exchange_fwd_load<0>(lo, hi, rt, tmb, tmb + (16u << 16), 0);
-        tm_unpack(xb, lo, hi);
-        const double2 E0 = make_double2(r3[0], r3[1]), E1 = make_double2(r3[2], r3[3]);
-        fwd_p3b(xa, E0, E1);
-        fwd_p3b(xb, E0, E1);
-    }
-
     template <bool DEFER_LAST, class Barrier>
     __device__ __forceinline__ void inverse2(double2 (&xa)[8], double2 (&xb)[8], double2 *bufa, double2 *bufb,
                                              const Barrier &bar) const {
