@@ -51,7 +51,7 @@ __device__ __forceinline__ void tmem_ld4(uint32_t addr, double2 (&v)[4]) {
 }
 
 // TMEM columns of one warp
-constexpr int kTmAcc0 = 0, kTmAcc1 = 64, kTmStash = 128, kTmColsPerWarp = 256;
+constexpr int kTmAcc0 = 0, kTmAcc1 = 64, kTmStash = 128, kTm16ColsPerWarp = 256;
 
 // Rows for the single-step test kernel: straight from global memory, layout [col][r][lane]
 struct GlobalRows16 {
@@ -256,7 +256,7 @@ __global__ void __launch_bounds__(32 * G, 1) k_blind_rotate16(const DeviceKey ke
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();  // bara visible; barriers initialised; TMEM base published
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tm = *tm_slot + (((uint32_t)(g & 3) * 32u) << 16) + (uint32_t)(g >> 2) * kTmColsPerWarp;
+    const uint32_t tm = *tm_slot + (((uint32_t)(g & 3) * 32u) << 16) + (uint32_t)(g >> 2) * kTm16ColsPerWarp;
 
     // ---- ACC = (0, X^{2N-barb} * mu*(1+X+...+X^{N-1}))   (lwe-bootstrapping-functions-fft.cpp:146-148)
     if (live) {

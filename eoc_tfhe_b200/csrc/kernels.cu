@@ -24,6 +24,9 @@
 #include <mutex>
 #include <math.h>
 #include <stdlib.h>
+#ifdef B200_BR_PROFILE
+#include <cstdio>
+#endif
 
 namespace b200 {
 
@@ -259,10 +262,26 @@ __device__ __forceinline__ void tma_load_row_pair(void *dst, const void *src, ui
 template <int STAGES>
 struct RingState {                 // lives in shared memory
     uint64_t full[STAGES];         // TMA completion barriers
-    int done[STAGES];              // warps that finished reading the stage's current contents
+    union {
+        uint64_t empty[STAGES];    // consumer barriers: one arrival per consumer warp and use of the stage (RingRows<.., true>)
+        int done[STAGES];          // the same as a plain counter (round-1 experiment kernels)
+    };
 };
+// One arrival on a consumer barrier; true for the arrival that completes the phase (the barrier then re-arms itself).
+// The returned state is the barrier BEFORE the arrival, so a pending count of 1 means "I am the last".  The arrival
+// is a release at CTA scope: no separate fence, and nobody resets a counter.
+__device__ __forceinline__ bool mbar_arrive_is_last(uint64_t *bar) {
+    uint64_t state;
+    uint32_t pending;
+    asm volatile("mbarrier.arrive.shared::cta.b64 %0, [%1];" : "=l"(state) : "r"(smem_u32(bar)) : "memory");
+    asm volatile("mbarrier.pending_count.b64 %0, %1;" : "=r"(pending) : "l"(state));
+    return pending == 1u;
+}
 
-template <int STAGES>
+#ifdef B200_BR_PROFILE
+__device__ long long g_br_prof[12];
+#endif
+template <int STAGES, bool MBAR = false>   // MBAR: stages handed back through mbarriers (st->empty) instead of fence + atomic counter
 struct RingRows {
     unsigned char *ring;           // [STAGES][kStageBytes]
     RingState<STAGES> *st;
@@ -281,6 +300,11 @@ struct RingRows {
     __device__ __forceinline__ void release(int rp) const {
         const int q = seq0 + rp, s = q % STAGES;
         __syncwarp();
+        if (MBAR) {
+            if (lane0 && mbar_arrive_is_last(&st->empty[s]) && q + STAGES < total)
+                tma_load_row_pair(ring + (size_t)s * kStageBytes, bk + (size_t)(q + STAGES) * 2 * kM, &st->full[s]);
+            return;
+        }
         if (lane0) {
             __threadfence_block();
             if (atomicAdd(&st->done[s], 1) == warps - 1) {
@@ -294,6 +318,15 @@ struct RingRows {
     // them -- the counter of the first -- and the last warp refills the n stages
     __device__ __forceinline__ void release_n(int rp, int n) const {
         const int q = seq0 + rp, s = q % STAGES;
+        if (MBAR) {
+            __syncwarp();
+            if (lane0 && mbar_arrive_is_last(&st->empty[s]))
+                for (int i = 0; i < n; ++i)
+                    if (q + i + STAGES < total)
+                        tma_load_row_pair(ring + (size_t)((q + i) % STAGES) * kStageBytes, bk + (size_t)(q + i + STAGES) * 2 * kM,
+                                          &st->full[(q + i) % STAGES]);
+            return;
+        }
         __syncwarp();
         if (lane0) {
             __threadfence_block();
@@ -524,6 +557,13 @@ __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int
 // the 64 accumulator registers exist only inside a MAC (half of them at a time) and inside the inverse transforms,
 // so six groups per SM have about 40 registers per thread more for the transforms than with resident accumulators.
 // One tcgen05.st + one tcgen05.ld of 256 bytes per thread per step at l = 2 (three of each at l = 3).
+#ifdef B200_BR_PROFILE   // phase clocks of thread 0 of CTA 0 (scratch builds only; scratch/prof_br.sh)
+#define BR_T(k) do { if (prof_on) { const long long now_ = clock64(); g_br_prof[k] += now_ - last_; last_ = now_; } } while (0)
+#define BR_T_BEGIN const bool prof_on = blockIdx.x == 0 && threadIdx.x == 0; long long last_ = clock64()
+#else
+#define BR_T(k) do { } while (0)
+#define BR_T_BEGIN do { } while (0)
+#endif
 template <int L, int BGBIT, int MODE, class Barrier, class Rows>
 __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *bufs, const int a, const Rows &rows,
                                                       const FftTmAcc &fft, const Barrier &bar) {
@@ -537,6 +577,7 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
     for (int p = 0; p < L; ++p) offset += HALF << (32 - (p + 1) * BGBIT);
 
     double2 acc0[8], acc1[8];   // defined by the last MAC event only
+    BR_T_BEGIN;
 
     // one half (registers 4h .. 4h+3) of a MAC event over NX rows: c += x . key
     auto mac_half = [&](double2 (&c0)[4], double2 (&c1)[4], const double2 (&x)[8], const double2 *row, int h) {
@@ -560,6 +601,7 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
     auto mac_event = [&](const int ev, const double2 (&xa)[8], const double2 (*xb)[8], const int rp) {
         const double2 *rowa = rows.acquire(rp) + t;
         const double2 *rowb = xb ? rows.acquire(rp + 1) + t : nullptr;
+        BR_T(7);
         if (ev > 0) tm_wait_st();
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -583,6 +625,7 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
                            c0[2].x, c0[2].y, c1[2].x, c1[2].y, c0[3].x, c0[3].y, c1[3].x, c1[3].y);
             }
         }
+        BR_T(8);
         rows.release_n(rp, xb ? 2 : 1);
     };
 
@@ -613,8 +656,11 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
             if (p + 1 < L) {
                 double2 xb[8];
                 digits_pretwisted<BGBIT>(xb, dv, shift - BGBIT);
+                BR_T(0);
                 fft.template forward2<true>(xa, xb, bufs, bufs + kBuf, bar);
+                BR_T(1);
                 mac_event(ev, xa, &xb, q * L + p);
+                BR_T(2);
             } else {
                 fft.template forward<true>(xa, bufs, bar);
                 mac_event(ev, xa, nullptr, q * L + p);
@@ -622,7 +668,9 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
         }
     }
     bar();
+    BR_T(3);
     fft.template inverse2<true>(acc0, acc1, bufs, bufs + kBuf, bar);
+    BR_T(4);
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         const int j = t + 64 * r;
@@ -632,7 +680,9 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
         if (MODE == 0) { ACC[j] += lo0; ACC[j + kM] += hi0; ACC[kN + j] += lo1; ACC[kN + j + kM] += hi1; }
         else           { ACC[j] = lo0;  ACC[j + kM] = hi0;  ACC[kN + j] = lo1;  ACC[kN + j + kM] = hi1; }
     }
+    BR_T(5);
     bar();  // accumulator complete before the next step's rotated reads; exchange buffers free
+    BR_T(6);
 }
 template <int L, int BGBIT, int MODE, class Barrier, class Rows>
 __device__ __forceinline__ void cmux_step(int32_t *ACC, double2 *bufs, const int a, const Rows &rows,
@@ -772,7 +822,9 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
     constexpr int KPL = 2 * L;
     unsigned char *ring = smem;                                                       // [stages][16 KiB]
     RingState<STAGES> *st = reinterpret_cast<RingState<STAGES> *>(smem + STAGES * kStageBytes);
-    const int g = threadIdx.x >> 6, t = threadIdx.x & 63;
+    // the group index is the same in every lane of a warp; the reduction tells the compiler, so that everything derived
+    // from it (accumulator / buffer / tensor-memory bases, barrier ids, the group's item) is uniform-datapath work
+    const int g = (int)__reduce_max_sync(0xffffffffu, threadIdx.x >> 6), t = threadIdx.x & 63;
     unsigned char *mine = smem + STAGES * kStageBytes + 128 + (size_t)g * group_smem_bytes<FFT>();
     int32_t *ACC = reinterpret_cast<int32_t *>(mine);                                // [2][1024]
     double2 *bufs = reinterpret_cast<double2 *>(mine + 2 * kN * 4);                  // [2][576 | 512]
@@ -780,6 +832,7 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
     const double2 *bkfft = UsesTm<FFT>::value ? key.bkfft_tm : key.bkfft;
     uint32_t *tm_slot_p = reinterpret_cast<uint32_t *>(smem + STAGES * kStageBytes + 120);   // behind the ring state
     uint32_t tm = 0;
+    static_assert(sizeof(RingState<STAGES>) <= 120, "ring state: 120 bytes before the tensor-memory slot");
     static_assert(!UsesTm<FFT>::value || TmShared<FFT>::value + ((2 * G + 3) / 4) * TmWindow<FFT>::value <= 512, "tensor-memory columns of the warps sharing a lane quarter");
     if (UsesTm<FFT>::value) tm = tm_alloc_cta(tm_slot_p, TmWindow<FFT>::value, TmShared<FFT>::value);
 
@@ -790,7 +843,7 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
     const int total = n * KPL;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; ++s) { mbar_init(&st->full[s], 1); st->done[s] = 0; }
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&st->full[s], 1); mbar_init(&st->empty[s], 2 * G); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         for (int s = 0; s < STAGES && s < total; ++s)
@@ -848,7 +901,7 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
     // ---- blind rotation (lwe-bootstrapping-functions-fft.cpp:88-112)
     int lane_id = threadIdx.x & 31;
     asm volatile("" : "+r"(lane_id));   // keep it in a register: the compiler otherwise re-reads SR_TID in the loop
-    RingRows<STAGES> rows{ring, st, bkfft, 0, total, 2 * G, lane_id == 0};
+    RingRows<STAGES, true> rows{ring, st, bkfft, 0, total, 2 * G, lane_id == 0};
 #pragma unroll 1
     for (int i = 0; i < n; ++i) {
         rows.seq0 = i * KPL;
@@ -874,6 +927,13 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const DeviceKey key,
         if (t == 0) u[kN] = ACC[kN];
     }
     if (UsesTm<FFT>::value) tm_free_cta(tm_slot_p);
+#ifdef B200_BR_PROFILE
+    if (blockIdx.x == 0 && threadIdx.x == 0 && PairEvents<FFT>::value) {
+        printf("tmacc group 0, clk per step (n = %d): decompose+digits %lld forward2 %lld mac event %lld | bar %lld inverse2 %lld round+update %lld bar %lld || inside mac event: acquire %lld compute %lld (release = rest: syncwarp %lld fence %lld atomic %lld)\n",
+               n, g_br_prof[0] / n, g_br_prof[1] / n, g_br_prof[2] / n, g_br_prof[3] / n, g_br_prof[4] / n, g_br_prof[5] / n, g_br_prof[6] / n, g_br_prof[7] / n, g_br_prof[8] / n, g_br_prof[9] / n, g_br_prof[10] / n, g_br_prof[11] / n);
+        for (int k = 0; k < 12; ++k) g_br_prof[k] = 0;
+    }
+#endif
 }
 
 }  // namespace b200
@@ -1471,7 +1531,12 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
         e = br_wide_tmacc() ? br_launch_tm<2, 10, 6, FftTmAcc>(key, a, s) : br_launch<2, 10, 6>(key, a, s);
     } else
     if (key.l == 2 && key.Bgbit == 10) BR_LAUNCH(2, 10);
-    else if (key.l == 3 && key.Bgbit == 7) BR_LAUNCH(3, 7);
+    else if (key.l == 3 && key.Bgbit == 7) {
+        // l = 3 in 'auto': four groups per CTA with the tensor-memory exchanges ("tm": 260.8 ms per 29,600 rotations
+        // against 265.1 for the shared-memory transform; parked accumulators do not pay here: 267-290 ms)
+        if (br_variant_raw() == kVarAuto && a.items > sms * 4) e = br_launch_tm<3, 7, 4>(key, a, s);
+        else BR_LAUNCH(3, 7);
+    }
     else if (key.l == 2 && key.Bgbit == 8) BR_LAUNCH(2, 8);
     else if (key.l == 1 && key.Bgbit == 16) BR_LAUNCH(1, 16);
     else if (key.l == 4 && key.Bgbit == 6) BR_LAUNCH(4, 6);
@@ -1504,7 +1569,8 @@ cudaError_t launch_cmux_test(const DeviceKey &key, int32_t *d_acc, int bk_index,
         return cudaGetLastError();
     }
 #endif
-    if ((br_variant_raw() >= 9 && br_variant_raw() <= 11) || (br_variant_raw() == kVarAuto && key.l == 2 && key.Bgbit == 10)) {
+    if ((br_variant_raw() >= 9 && br_variant_raw() <= 11) ||
+        (br_variant_raw() == kVarAuto && ((key.l == 2 && key.Bgbit == 10) || (key.l == 3 && key.Bgbit == 7)))) {
         int dev = 0;
         cudaGetDevice(&dev);
         const unsigned grid = (unsigned)std::min<int64_t>(count, sm_count_of(dev));
