@@ -515,7 +515,7 @@ def main_b200(args):
                          "ms_per_launch": br, "share_of_step": br / ms_per_step,
                          "peak_source": "DFMA-chain kernel of this library timed live (MEASURED_PEAKS.json has no FP64 figure)",
                          "algorithmic_flop_per_bootstrap": FLOP_PER_BOOTSTRAP_P80},
-            "roofline_keyswitch": {"bound": "int32 add issue", "kernel": "k_keyswitch_tma<64,8,8,2,0,126>", "achieved": ks_adds / (ksm * 1e-3) / 1e12,
+            "roofline_keyswitch": {"bound": "int32 add issue", "kernel": "k_keyswitch_tma<64,8,8,2,4,126>", "achieved": ks_adds / (ksm * 1e-3) / 1e12,
                                    "peak": iadd_peak, "unit": "Tadd/s", "frac": ks_adds / (ksm * 1e-3) / 1e12 / iadd_peak if iadd_peak else None,
                                    "traffic": ncu_traffic("k_keyswitch_tma"), "ms_per_launch": ksm, "share_of_step": ksm / ms_per_step,
                                    "peak_source": "int32 add-chain kernel of this library timed live",

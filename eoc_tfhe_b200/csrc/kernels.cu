@@ -1639,14 +1639,15 @@ cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaS
         const int64_t per_cta = small ? 64 : 40;
         const bool full = a.items >= sms * per_cta;
         if (ks_sel == 2 || a.items >= sms * 20) {
-            // Row choice (B200_KS_MODE, A/B only): 0 = uniform 3-way branch per sample and digit (default);
-            // 1 / 2 = one 16-way switch per sample pair / digit pair (nvcc lowers it to a compare tree);
-            // 3 / 4 = the same through one brx.idx jump table each.  All bit-identical; 65,536 samples take
-            // 25.7 / 29.7 / 27.9 / 25.6 / 25.3 ms: fewer instructions do not help, the bound is the latency of
-            // the decisions one warp makes in sequence.
-            static const int ks_mode = [] { const char *m = getenv("B200_KS_MODE"); return m ? atoi(m) : 0; }();
+            // Row choice (B200_KS_MODE): 4 (default) = one brx.idx jump table per sample and DIGIT PAIR, both rows leaving
+            // in one three-input add; 0 = uniform 3-way branch per sample and digit; 1 / 2 = one 16-way switch per sample
+            // pair / digit pair (nvcc lowers it to a compare tree); 3 = sample pairs through a jump table.  All
+            // bit-identical; 65,536 samples at the 80-bit set: 23.5 / 24.8 / 28.1 / 26.7 / 24.7 ms.
+            static const int ks_mode = [] { const char *m = getenv("B200_KS_MODE"); return m ? atoi(m) : 4; }();
             cudaError_t e;
-            if (small && full && stride4 == 126) {        // 80-bit set: row stride known at compile time
+            if (small && stride4 == 126) {                // 80-bit set: row stride known at compile time
+                if (!full) e = ks_mode == 4 ? ks2_launch<64, 4, 8, 2, 4, 126>(key, a, s) : ks2_launch<64, 4, 8, 2, 0, 126>(key, a, s);
+                else
                 e = ks_mode == 1 ? ks2_launch<64, 8, 8, 2, 1, 126>(key, a, s)
                   : ks_mode == 2 ? ks2_launch<64, 8, 8, 2, 2, 126>(key, a, s)
                   : ks_mode == 3 ? ks2_launch<64, 8, 8, 2, 3, 126>(key, a, s)
@@ -1654,9 +1655,10 @@ cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaS
                                  : ks2_launch<64, 8, 8, 2, 0, 126>(key, a, s);
             } else if (small)
                 e = full ? ks2_launch<64, 8, 8, 2>(key, a, s) : ks2_launch<64, 4, 8, 2>(key, a, s);
-            else if (stride4 == 158)                      // 128-bit set
-                e = full ? ks2_launch<96, 5, 8, 2, 0, 158>(key, a, s) : ks2_launch<96, 3, 8, 2, 0, 158>(key, a, s);
-            else
+            else if (stride4 == 158) {                    // 128-bit set
+                if (ks_mode == 4) e = full ? ks2_launch<96, 5, 8, 2, 4, 158>(key, a, s) : ks2_launch<96, 3, 8, 2, 4, 158>(key, a, s);
+                else e = full ? ks2_launch<96, 5, 8, 2, 0, 158>(key, a, s) : ks2_launch<96, 3, 8, 2, 0, 158>(key, a, s);
+            } else
                 e = full ? ks2_launch<96, 5, 8, 2>(key, a, s) : ks2_launch<96, 3, 8, 2>(key, a, s);
             if (e != cudaSuccess) return e;
             COUNT_LAUNCH();

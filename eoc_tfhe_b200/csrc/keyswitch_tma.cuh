@@ -25,13 +25,13 @@ constexpr int kKs2RowsPerStage = 12;  // half of the 24 rows of one coefficient 
 
 template <int S> struct Ks2State {   // S = samples per CTA
     uint64_t full[kKs2Stages];
-    int done[kKs2Stages];
+    uint64_t empty[kKs2Stages];    // consumer barriers: one arrival per warp and use of the stage
     int nz[S];
     int32_t bterm[S];
     int32_t outrow[S];
 };
 
-__host__ __device__ constexpr int ks2_state_bytes(int S) { return ((kKs2Stages * 12 + S * 12) + 127) / 128 * 128; }
+__host__ __device__ constexpr int ks2_state_bytes(int S) { return ((kKs2Stages * 16 + S * 12) + 127) / 128 * 128; }
 __host__ __device__ constexpr int ks2_smem_bytes(int S, int stride) {
     return kKs2Stages * kKs2RowsPerStage * stride * 4 + 2 * kKs2Chunk * S * 2 + ks2_state_bytes(S);
 }
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keys
     const unsigned char *tab = reinterpret_cast<const unsigned char *>(key.ks);
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kKs2Stages; ++s) { mbar_init(&st->full[s], 1); st->done[s] = 0; }
+        for (int s = 0; s < kKs2Stages; ++s) { mbar_init(&st->full[s], 1); mbar_init(&st->empty[s], WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         for (int s = 0; s < kKs2Stages && s < total; ++s) {
@@ -238,19 +238,13 @@ __global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keys
                         }
                     }
                 }
-                // hand the stage back; the last warp of the CTA to do so refills it
+                // hand the stage back (one mbarrier arrival per warp); the arrival that completes the phase refills it
                 __syncwarp();
-                if ((threadIdx.x & 31) == 0) {
-                    __threadfence_block();
-                    if (atomicAdd(&st->done[s], 1) == WARPS - 1) {
-                        st->done[s] = 0;
-                        if (q + kKs2Stages < total) {
-                            const uint32_t b = smem_u32(&st->full[s]), d = smem_u32(ring + (size_t)s * stage_bytes);
-                            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(stage_bytes) : "memory");
-                            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                                         ::"r"(d), "l"(tab + (size_t)(q + kKs2Stages) * stage_bytes), "r"(stage_bytes), "r"(b) : "memory");
-                        }
-                    }
+                if ((threadIdx.x & 31) == 0 && mbar_arrive_is_last(&st->empty[s]) && q + kKs2Stages < total) {
+                    const uint32_t b = smem_u32(&st->full[s]), d = smem_u32(ring + (size_t)s * stage_bytes);
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(stage_bytes) : "memory");
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                 ::"r"(d), "l"(tab + (size_t)(q + kKs2Stages) * stage_bytes), "r"(stage_bytes), "r"(b) : "memory");
                 }
             }
         }

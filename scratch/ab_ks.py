@@ -5,8 +5,8 @@ import os
 import sys
 import numpy as np, torch
 sys.path.insert(0, ".")
-from eoc_tfhe_b200 import CloudKey, PARAMS_80, GateOp
-P = PARAMS_80
+from eoc_tfhe_b200 import CloudKey, PARAMS_80, PARAMS_128, GateOp
+P = PARAMS_128 if (len(sys.argv) > 2 and sys.argv[2] == "128") else PARAMS_80
 count = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
 rng = np.random.default_rng(0)
 bk = rng.integers(-2**31, 2**31, size=P.bk_shape, dtype=np.int64).astype(np.int32)
