@@ -232,6 +232,8 @@ struct GlobalRows {
     __device__ __forceinline__ int release_begin(int) const { return 0; }
     __device__ __forceinline__ void release_end(int, int) const {}
     __device__ __forceinline__ void release_n(int, int) const {}
+    __device__ __forceinline__ uint64_t release_n_begin(int) const { return 0; }
+    __device__ __forceinline__ void release_n_end(int, int, uint64_t) const {}
 };
 
 constexpr int kStageBytes = 2 * kM * 16;  // one row pair
@@ -337,6 +339,28 @@ struct RingRows {
                         tma_load_row_pair(ring + (size_t)((q + i) % STAGES) * kStageBytes, bk + (size_t)(q + i + STAGES) * 2 * kM,
                                           &st->full[(q + i) % STAGES]);
             }
+        }
+    }
+    // release_n in two halves (MBAR): the arrival is issued at once, its answer -- am I the last? -- is looked at later,
+    // so the barrier's round trip (lane 0 needs the old state; the whole warp would wait for lane 0 at the
+    // reconvergence point) overlaps with the caller's next piece of work.
+    __device__ __forceinline__ uint64_t release_n_begin(int rp) const {
+        const int q = seq0 + rp, s = q % STAGES;
+        uint64_t state = 0;
+        __syncwarp();
+        if (lane0) asm volatile("mbarrier.arrive.shared::cta.b64 %0, [%1];" : "=l"(state) : "r"(smem_u32(&st->empty[s])) : "memory");
+        return state;
+    }
+    __device__ __forceinline__ void release_n_end(int rp, int n, uint64_t state) const {
+        const int q = seq0 + rp;
+        if (lane0) {
+            uint32_t pending;
+            asm volatile("mbarrier.pending_count.b64 %0, %1;" : "=r"(pending) : "l"(state));
+            if (pending == 1u)
+                for (int i = 0; i < n; ++i)
+                    if (q + i + STAGES < total)
+                        tma_load_row_pair(ring + (size_t)((q + i) % STAGES) * kStageBytes, bk + (size_t)(q + i + STAGES) * 2 * kM,
+                                          &st->full[(q + i) % STAGES]);
         }
     }
     // The same in two halves, so that the shared-memory atomic's round trip (lane 0 needs the old count to know
@@ -577,6 +601,8 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
     for (int p = 0; p < L; ++p) offset += HALF << (32 - (p + 1) * BGBIT);
 
     double2 acc0[8], acc1[8];   // defined by the last MAC event only
+    uint64_t pending_release = 0;   // state of the ring's consumer barrier before this warp's last arrival (lane 0)
+    int pending_rp = 0, pending_n = 0;
     BR_T_BEGIN;
 
     // one half (registers 4h .. 4h+3) of a MAC event over NX rows: c += x . key
@@ -626,7 +652,10 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
             }
         }
         BR_T(8);
-        rows.release_n(rp, xb ? 2 : 1);
+        // the arrival goes out now; whether it was the last one (-> refill) is looked at after the next piece of work
+        pending_release = rows.release_n_begin(rp);
+        pending_rp = rp;
+        pending_n = xb ? 2 : 1;
     };
 
 #pragma unroll
@@ -648,6 +677,7 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
 #pragma unroll
         for (int p = 0; p < L; p += 2) {
             const int ev = q * ((L + 1) / 2) + p / 2;
+            if (ev > 0) rows.release_n_end(pending_rp, pending_n, pending_release);
             if (ev > 0) bar();   // every thread of the group has read the previous transforms' exchange buffers
             const int shift = 32 - (p + 1) * BGBIT;
             // digits as exact doubles, registers 4..7 pre-twisted by the level-0 root on the integer side
@@ -667,6 +697,7 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
             }
         }
     }
+    rows.release_n_end(pending_rp, pending_n, pending_release);
     bar();
     BR_T(3);
     fft.template inverse2<true>(acc0, acc1, bufs, bufs + kBuf, bar);
