@@ -1669,15 +1669,30 @@ cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaS
         // Batches that cannot fill 148 CTAs of 64 samples use CTAs of 32 (two per SM) down to 2,960 samples (below that the gather kernel is as fast).
         const int64_t per_cta = small ? 64 : 40;
         const bool full = a.items >= sms * per_cta;
-        if (ks_sel == 2 || a.items >= sms * 20) {
+        // (with the coefficient range split up to 16 ways the streaming kernel beats the gather kernel from about a
+        // hundred samples on: 592 samples 0.82 -> 0.2 ms; below that the gather kernel's 256-way split wins)
+        static const int64_t ks_min = [] { const char *m = getenv("B200_KS_MIN"); return (int64_t)(m ? atoi(m) : 96); }();
+        if (ks_sel == 2 || a.items >= ks_min) {
             // Row choice (B200_KS_MODE): 4 (default) = one brx.idx jump table per sample and DIGIT PAIR, both rows leaving
             // in one three-input add; 0 = uniform 3-way branch per sample and digit; 1 / 2 = one 16-way switch per sample
             // pair / digit pair (nvcc lowers it to a compare tree); 3 = sample pairs through a jump table.  All
             // bit-identical; 65,536 samples at the 80-bit set: 23.5 / 24.8 / 28.1 / 26.7 / 24.7 ms.
             static const int ks_mode = [] { const char *m = getenv("B200_KS_MODE"); return m ? atoi(m) : 4; }();
             cudaError_t e;
+            // Batches that leave SMs (or second CTA slots) empty cut the coefficient range instead: nsplit CTAs per
+            // sample tile, partial sums combined with integer atomics in zeroed rows (4,096 samples: 2.94 -> 1.6 ms)
+            int nsplit = 1;
+            if (!full) {
+                const int64_t ctas = (a.items + (small ? 32 : 24) - 1) / (small ? 32 : 24), slots = small ? 2 * sms : sms;
+                static const int ks_split = [] { const char *m = getenv("B200_KS_SPLIT"); return m ? atoi(m) : 16; }();
+                nsplit = (int)std::max<int64_t>(1, std::min<int64_t>(ks_split, slots / ctas));
+                if (nsplit > 1) {
+                    k_zero_rows<<<(unsigned)a.items, 128, 0, s>>>(a.out, a.desc, a.items, key.n + 1);
+                    COUNT_LAUNCH();
+                }
+            }
             if (small && stride4 == 126) {                // 80-bit set: row stride known at compile time
-                if (!full) e = ks_mode == 4 ? ks2_launch<64, 4, 8, 2, 4, 126>(key, a, s) : ks2_launch<64, 4, 8, 2, 0, 126>(key, a, s);
+                if (!full) e = ks_mode == 4 ? ks2_launch<64, 4, 8, 2, 4, 126>(key, a, s, nsplit) : ks2_launch<64, 4, 8, 2, 0, 126>(key, a, s, nsplit);
                 else
                 e = ks_mode == 1 ? ks2_launch<64, 8, 8, 2, 1, 126>(key, a, s)
                   : ks_mode == 2 ? ks2_launch<64, 8, 8, 2, 2, 126>(key, a, s)
@@ -1685,12 +1700,12 @@ cudaError_t launch_keyswitch(const DeviceKey &key, const KeySwitchArgs &a, cudaS
                   : ks_mode == 4 ? ks2_launch<64, 8, 8, 2, 4, 126>(key, a, s)
                                  : ks2_launch<64, 8, 8, 2, 0, 126>(key, a, s);
             } else if (small)
-                e = full ? ks2_launch<64, 8, 8, 2>(key, a, s) : ks2_launch<64, 4, 8, 2>(key, a, s);
+                e = full ? ks2_launch<64, 8, 8, 2>(key, a, s) : ks2_launch<64, 4, 8, 2>(key, a, s, nsplit);
             else if (stride4 == 158) {                    // 128-bit set
-                if (ks_mode == 4) e = full ? ks2_launch<96, 5, 8, 2, 4, 158>(key, a, s) : ks2_launch<96, 3, 8, 2, 4, 158>(key, a, s);
-                else e = full ? ks2_launch<96, 5, 8, 2, 0, 158>(key, a, s) : ks2_launch<96, 3, 8, 2, 0, 158>(key, a, s);
+                if (ks_mode == 4) e = full ? ks2_launch<96, 5, 8, 2, 4, 158>(key, a, s) : ks2_launch<96, 3, 8, 2, 4, 158>(key, a, s, nsplit);
+                else e = full ? ks2_launch<96, 5, 8, 2, 0, 158>(key, a, s) : ks2_launch<96, 3, 8, 2, 0, 158>(key, a, s, nsplit);
             } else
-                e = full ? ks2_launch<96, 5, 8, 2>(key, a, s) : ks2_launch<96, 3, 8, 2>(key, a, s);
+                e = full ? ks2_launch<96, 5, 8, 2>(key, a, s) : ks2_launch<96, 3, 8, 2>(key, a, s, nsplit);
             if (e != cudaSuccess) return e;
             COUNT_LAUNCH();
             return cudaGetLastError();

@@ -82,18 +82,25 @@ __global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keys
     const int grp = threadIdx.x / TG, t = threadIdx.x - grp * TG;
     const int64_t item0 = (int64_t)blockIdx.x * S;
     const uint32_t prec_offset = 1u << (32 - (1 + 2 * T));
-    const int total = Nin * 2;                       // half-coefficient slabs
+    // gridDim.y > 1: the coefficient range is cut into gridDim.y pieces of whole 64-coefficient chunks, one CTA each;
+    // the partial sums meet in the output rows through integer atomics (wrap-around addition: bit-exact in any order),
+    // the rows are zeroed by the launcher.  Batches that cannot fill the SMs with whole-range CTAs use it.
+    const int nchunks = (Nin + kKs2Chunk - 1) / kKs2Chunk;
+    const int nsplit = (int)gridDim.y, split = (int)blockIdx.y;
+    const int chunk0 = nchunks * split / nsplit, chunk1 = nchunks * (split + 1) / nsplit;
+    const int q0 = chunk0 * kKs2Chunk * 2;                                   // first half-coefficient slab of this CTA
+    const int total = min(chunk1 * kKs2Chunk, Nin) * 2;                     // one past its last
     const unsigned char *tab = reinterpret_cast<const unsigned char *>(key.ks);
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kKs2Stages; ++s) { mbar_init(&st->full[s], 1); mbar_init(&st->empty[s], WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        for (int s = 0; s < kKs2Stages && s < total; ++s) {
+        for (int s = 0; s < kKs2Stages && q0 + s < total; ++s) {
             const uint32_t b = smem_u32(&st->full[s]), d = smem_u32(ring + (size_t)s * stage_bytes);
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(stage_bytes) : "memory");
             asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                         ::"r"(d), "l"(tab + (size_t)s * stage_bytes), "r"(stage_bytes), "r"(b) : "memory");
+                         ::"r"(d), "l"(tab + (size_t)(q0 + s) * stage_bytes), "r"(stage_bytes), "r"(b) : "memory");
         }
     }
     // per-sample constants: b term (lwe-keyswitch-functions.cpp:232) and destination row
@@ -118,7 +125,7 @@ __global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keys
 
     // digit pre-pass of one chunk (lwe-keyswitch-functions.cpp:122-125): top 2T bits of a_i + prec_offset
     auto prepass = [&](int chunk) {
-        uint16_t *dst = dig + (size_t)(chunk & 1) * kKs2Chunk * S;
+        uint16_t *dst = dig + (size_t)((chunk - chunk0) & 1) * kKs2Chunk * S;
         const int i0 = chunk * kKs2Chunk;
         for (int idx = threadIdx.x; idx < S * kKs2Chunk; idx += TG * NG) {
             const int g = idx / kKs2Chunk, ii = idx - g * kKs2Chunk;
@@ -138,7 +145,7 @@ __global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keys
             dst[ii * S + g] = (uint16_t)packed;
         }
     };
-    prepass(0);
+    prepass(chunk0);
     __syncthreads();
 
     int4 acc[SG][NC];
@@ -151,11 +158,10 @@ __global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keys
 #pragma unroll
     for (int c = 0; c < NC; ++c) { has[c] = t + TG * c < stride4; col[c] = has[c] ? t + TG * c : 0; }
 
-    const int nchunks = (Nin + kKs2Chunk - 1) / kKs2Chunk;
 #pragma unroll 1
-    for (int chunk = 0; chunk < nchunks; ++chunk) {
-        if (chunk + 1 < nchunks) prepass(chunk + 1);   // the other buffer; made visible by the barrier below
-        const uint16_t *dg = dig + (size_t)(chunk & 1) * kKs2Chunk * S + grp * SG;
+    for (int chunk = chunk0; chunk < chunk1; ++chunk) {
+        if (chunk + 1 < chunk1) prepass(chunk + 1);   // the other buffer; made visible by the barrier below
+        const uint16_t *dg = dig + (size_t)((chunk - chunk0) & 1) * kKs2Chunk * S + grp * SG;
         const int icnt = min(kKs2Chunk, Nin - chunk * kKs2Chunk);
 #pragma unroll 1
         for (int ii = 0; ii < icnt; ++ii) {
@@ -173,8 +179,8 @@ __global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keys
             for (int k = 0; k < SG / 2; ++k) w[k] = __reduce_or_sync(0xffffffffu, w[k]);
 #pragma unroll 1
             for (int jh = 0; jh < 2; ++jh) {
-                const int q = (chunk * kKs2Chunk + ii) * 2 + jh, s = q % kKs2Stages;
-                mbar_wait(&st->full[s], (uint32_t)(q / kKs2Stages) & 1u);
+                const int q = (chunk * kKs2Chunk + ii) * 2 + jh, s = (q - q0) % kKs2Stages;
+                mbar_wait(&st->full[s], (uint32_t)((q - q0) / kKs2Stages) & 1u);
                 const int4 *rows = reinterpret_cast<const int4 *>(ring + (size_t)s * stage_bytes);
                 if (MODE == 0) {
 #pragma unroll
@@ -265,7 +271,11 @@ __global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keys
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 const int colx = cbase + c;
-                if (colx < n1) o[colx] = vals[c] + (colx == key.n ? bt : 0);
+                if (colx < n1) {
+                    const int32_t v = vals[c] + ((colx == key.n && split == 0) ? bt : 0);
+                    if (nsplit == 1) o[colx] = v;
+                    else atomicAdd(o + colx, v);
+                }
             }
         }
     }
@@ -274,7 +284,7 @@ __global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keys
 }
 
 template <int TG, int NG, int SG, int NC, int MODE = 0, int STRIDE4 = 0>
-static cudaError_t ks2_launch(const DeviceKey &key, const KeySwitchArgs &a, cudaStream_t s) {
+static cudaError_t ks2_launch(const DeviceKey &key, const KeySwitchArgs &a, cudaStream_t s, int nsplit = 1) {
     static bool done[16] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
@@ -286,7 +296,7 @@ static cudaError_t ks2_launch(const DeviceKey &key, const KeySwitchArgs &a, cuda
         if (e != cudaSuccess) return e;
         if (dev < 16) done[dev] = true;
     }
-    const unsigned grid = (unsigned)((a.items + NG * SG - 1) / (NG * SG));
+    const dim3 grid((unsigned)((a.items + NG * SG - 1) / (NG * SG)), (unsigned)nsplit);
     k_keyswitch_tma<TG, NG, SG, NC, MODE, STRIDE4><<<grid, TG * NG, smem, s>>>(key, a);
     return cudaSuccess;
 }
