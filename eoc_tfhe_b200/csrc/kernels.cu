@@ -687,7 +687,15 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
                 double2 xb[8];
                 digits_pretwisted<BGBIT>(xb, dv, shift - BGBIT);
                 BR_T(0);
+#ifndef B200_SKEWED_PAIRS
+                // one after the other: with three warps per scheduler the other warps hide the exchange latency, and
+                // the simpler instruction stream schedules better than FftTm::forward2's skewed pair (308.9 -> 303.3 ms
+                // with the inverse below; the pair was worth 3 % when the kernel still had 168 registers and spills)
+                fft.template forward<true>(xa, bufs, bar);
+                fft.template forward<true>(xb, bufs + kBuf, bar);
+#else
                 fft.template forward2<true>(xa, xb, bufs, bufs + kBuf, bar);
+#endif
                 BR_T(1);
                 mac_event(ev, xa, &xb, q * L + p);
                 BR_T(2);
@@ -700,7 +708,12 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
     rows.release_n_end(pending_rp, pending_n, pending_release);
     bar();
     BR_T(3);
+#ifndef B200_SKEWED_PAIRS
+    fft.template inverse<true>(acc0, bufs, bar);
+    fft.template inverse<true>(acc1, bufs + kBuf, bar);
+#else
     fft.template inverse2<true>(acc0, acc1, bufs, bufs + kBuf, bar);
+#endif
     BR_T(4);
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
