@@ -678,7 +678,15 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
         for (int p = 0; p < L; p += 2) {
             const int ev = q * ((L + 1) / 2) + p / 2;
             if (ev > 0) rows.release_n_end(pending_rp, pending_n, pending_release);
+            // One after the other, the transforms of a pair alternate between the two exchange buffers and each has a
+            // group barrier between its writes and its reads: whoever writes a buffer again has passed the barrier of
+            // the transform in between, which every thread reaches only after its reads of that buffer -- no extra
+            // barrier.  Only an odd l leaves a lone transform last, and its buffer is the next one written.
+#ifdef B200_SKEWED_PAIRS
             if (ev > 0) bar();   // every thread of the group has read the previous transforms' exchange buffers
+#else
+            if ((L & 1) && q == 1 && p == 0) bar();
+#endif
             const int shift = 32 - (p + 1) * BGBIT;
             // digits as exact doubles, registers 4..7 pre-twisted by the level-0 root on the integer side
             double2 xa[8];
@@ -706,7 +714,11 @@ __device__ __forceinline__ void cmux_step_pairs_tmacc(int32_t *ACC, double2 *buf
         }
     }
     rows.release_n_end(pending_rp, pending_n, pending_release);
+#ifdef B200_SKEWED_PAIRS
     bar();
+#else
+    if (L & 1) bar();
+#endif
     BR_T(3);
 #ifndef B200_SKEWED_PAIRS
     fft.template inverse<true>(acc0, bufs, bar);
@@ -1576,9 +1588,9 @@ cudaError_t launch_blind_rotate(const DeviceKey &key, const BlindRotateArgs &a, 
     } else
     if (key.l == 2 && key.Bgbit == 10) BR_LAUNCH(2, 10);
     else if (key.l == 3 && key.Bgbit == 7) {
-        // l = 3 in 'auto': four groups per CTA with the tensor-memory exchanges ("tm": 260.8 ms per 29,600 rotations
-        // against 265.1 for the shared-memory transform; parked accumulators do not pay here: 267-290 ms)
-        if (br_variant_raw() == kVarAuto && a.items > sms * 4) e = br_launch_tm<3, 7, 4>(key, a, s);
+        // l = 3 in 'auto': four groups per CTA with the tensor-memory transform and parked accumulators (259.0 ms per
+        // 29,600 rotations; without parking, "tm", 261.5; shared-memory transform 265.1; six groups 282)
+        if (br_variant_raw() == kVarAuto && a.items > sms * 4) e = br_launch_tm<3, 7, 4, FftTmAcc>(key, a, s);
         else BR_LAUNCH(3, 7);
     }
     else if (key.l == 2 && key.Bgbit == 8) BR_LAUNCH(2, 8);
