@@ -97,20 +97,19 @@ __global__ void __launch_bounds__(128 * L, 1) k_blind_rotate_lat(const DeviceKey
 
         const int32_t *P = ACC + q * kN;
         double2 x[8];
+        {
+            uint32_t dv[16];   // (rotated difference) + decomposition offset, coefficient t + 64 rr
 #pragma unroll
-        for (int r = 0; r < 8; ++r) {
-            uint32_t dv[2];
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                const int j = t + 64 * r + kM * c;
+            for (int rr = 0; rr < 16; ++rr) {
+                const int j = t + 64 * rr;
                 const int m = (j - ai) & (2 * kN - 1);
                 int32_t v = P[m & (kN - 1)];
                 if (m & kN) v = -v;
-                dv[c] = (uint32_t)(v - P[j]) + offset;
+                dv[rr] = (uint32_t)(v - P[j]) + offset;
             }
-            x[r] = make_double2(digit_to_double<BGBIT>(dv[0], shift), digit_to_double<BGBIT>(dv[1], shift));
+            digits_pretwisted<BGBIT>(x, dv, shift);   // level 0 of the transform on the integer side
         }
-        negacyclic_forward(x, bufs + toggle * kBufElems, t, w2, w3, bar);
+        negacyclic_forward<true>(x, bufs + toggle * kBufElems, t, w2, w3, bar);
         toggle ^= 1;
 #pragma unroll
         for (int r = 0; r < 8; ++r) {

@@ -168,21 +168,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 * L, 1) k_blind_r
         LAT2_T(9);
 
         double2 x[8];
+        {
+            uint32_t dv[16];   // (rotated difference) + decomposition offset, coefficient t + 64 rr
 #pragma unroll
-        for (int r = 0; r < 8; ++r) {
-            uint32_t dv[2];
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                const int j = t + 64 * r + kM * c;
+            for (int rr = 0; rr < 16; ++rr) {
+                const int j = t + 64 * rr;
                 const int m = (j - ai) & (2 * kN - 1);
                 int32_t v = ACC[m & (kN - 1)];
                 if (m & kN) v = -v;
-                dv[c] = (uint32_t)(v - ACC[j]) + offset;
+                dv[rr] = (uint32_t)(v - ACC[j]) + offset;
             }
-            x[r] = make_double2(digit_to_double<BGBIT>(dv[0], shift), digit_to_double<BGBIT>(dv[1], shift));
+            digits_pretwisted<BGBIT>(x, dv, shift);   // level 0 of the transform on the integer side
         }
         LAT2_T(0);
-        fft.forward(x, buf, bar);
+        fft.template forward<true>(x, buf, bar);
         LAT2_T(1);
         // the partial for the peer first: it has the longer way.  Groups 0..l-2 hand theirs to group l-1 through
         // shared memory and a named barrier they only arrive at; group l-1 adds and pushes while the others go on

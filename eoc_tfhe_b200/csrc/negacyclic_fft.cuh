@@ -211,11 +211,12 @@ struct NamedBarrier64 {
 };
 
 // coefficients (pass-1 layout, x[r] = z_{t+64r}) -> evaluations (pass-3 layout, e = 8t + r)
-template <class Barrier>
+// PRE: x[4..7] arrive twisted by the level-0 root (digits_pretwisted)
+template <bool PRE = false, class Barrier>
 __device__ __forceinline__ void negacyclic_forward(double2 (&x)[8], double2 *buf, const int t,
                                                    const RootSet &w2, const RootSet &w3,
                                                    const Barrier &bar) {
-    fwd_radix8(x, c_tw.p1);
+    if (PRE) fwd_radix8_first_pretwisted(x); else fwd_radix8(x, c_tw.p1);
 #pragma unroll
     for (int r = 0; r < 8; ++r) buf[pad_idx(t + 64 * r)] = x[r];
     bar();

@@ -489,9 +489,9 @@ struct FftSmem {
         w2 = load_rootset(c_tw.p2[t >> 3]);
         w3 = load_rootset(c_tw.p3[t]);
     }
-    template <class Barrier>
+    template <bool PRE = false, class Barrier>
     __device__ __forceinline__ void forward(double2 (&x)[8], double2 *buf, const Barrier &bar) const {
-        negacyclic_forward(x, buf, t, w2, w3, bar);
+        negacyclic_forward<PRE>(x, buf, t, w2, w3, bar);
     }
     template <bool DEFER_LAST, class Barrier>
     __device__ __forceinline__ void inverse(double2 (&x)[8], double2 *buf, const Barrier &bar) const {
