@@ -781,10 +781,8 @@ __device__ __forceinline__ void cmux_step_single_tmacc(int32_t *ACC, double2 *bu
             if (ev > 0) bar();   // the partner warp has read the previous transform's exchange buffer
             const int shift = 32 - (p + 1) * BGBIT;
             double2 x[8];
-#pragma unroll
-            for (int r = 0; r < 8; ++r)
-                x[r] = make_double2(digit_to_double<BGBIT>(dv[r], shift), digit_to_double<BGBIT>(dv[r + 8], shift));
-            fft.forward(x, buf, bar);
+            digits_pretwisted<BGBIT>(x, dv, shift);   // level 0 of the transform on the integer side
+            fft.template forward<true>(x, buf, bar);
             const double2 *row = rows.acquire(ev) + t;
             if (ev > 0) tm_wait_st();
 #pragma unroll
