@@ -20,20 +20,23 @@
 namespace b200 {
 
 constexpr int kKs2Chunk = 64;       // coefficients per digit chunk
-constexpr int kKs2Stages = 4;
+constexpr int kKs2StagesMax = 6;
+// ring depth: the eight-group CTA of the 80-bit set takes six stages (65,536 samples 19.7 -> 19.3 ms); the smaller
+// shapes stay at four so that two of them fit an SM, and the 128-bit set's 30 KB stages gain nothing from more
+__host__ __device__ constexpr int ks2_stages(int ng) { return ng >= 8 ? 6 : 4; }
 constexpr int kKs2RowsPerStage = 12;  // half of the 24 rows of one coefficient (j = 0..3 or 4..7, h = 1..3)
 
 template <int S> struct Ks2State {   // S = samples per CTA
-    uint64_t full[kKs2Stages];
-    uint64_t empty[kKs2Stages];    // consumer barriers: one arrival per warp and use of the stage
+    uint64_t full[kKs2StagesMax];
+    uint64_t empty[kKs2StagesMax];    // consumer barriers: one arrival per warp and use of the stage
     int nz[S];
     int32_t bterm[S];
     int32_t outrow[S];
 };
 
-__host__ __device__ constexpr int ks2_state_bytes(int S) { return ((kKs2Stages * 16 + S * 12) + 127) / 128 * 128; }
-__host__ __device__ constexpr int ks2_smem_bytes(int S, int stride) {
-    return kKs2Stages * kKs2RowsPerStage * stride * 4 + 2 * kKs2Chunk * S * 2 + ks2_state_bytes(S);
+__host__ __device__ constexpr int ks2_state_bytes(int S) { return ((kKs2StagesMax * 16 + S * 12) + 127) / 128 * 128; }
+__host__ __device__ constexpr int ks2_smem_bytes(int S, int stride, int stages) {
+    return stages * kKs2RowsPerStage * stride * 4 + 2 * kKs2Chunk * S * 2 + ks2_state_bytes(S);
 }
 
 __device__ __forceinline__ void ks2_sub(int4 &a, const int4 &v) { a.x -= v.x; a.y -= v.y; a.z -= v.z; a.w -= v.w; }
@@ -71,7 +74,7 @@ template <int TG, int NG, int SG, int NC, int MODE = 0, int STRIDE4 = 0>
 __global__ void __launch_bounds__(TG * NG, (TG == 64 && NG <= 4) ? 2 : 1) k_keyswitch_tma(const DeviceKey key, const KeySwitchArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     static_assert(SG == 8 || SG == 16, "8 or 16 samples per group");
-    constexpr int T = 8, S = NG * SG, WARPS = TG * NG / 32;
+    constexpr int T = 8, S = NG * SG, WARPS = TG * NG / 32, kKs2Stages = ks2_stages(NG);
     const int Nin = key.N * key.k, n1 = key.n + 1;
     const int stride = STRIDE4 > 0 ? STRIDE4 * 4 : key.ks_stride, stride4 = stride >> 2;
     const int stage_bytes = kKs2RowsPerStage * stride * 4;
@@ -289,7 +292,7 @@ static cudaError_t ks2_launch(const DeviceKey &key, const KeySwitchArgs &a, cuda
     int dev = 0;
     cudaGetDevice(&dev);
     if (STRIDE4 > 0 && key.ks_stride != STRIDE4 * 4) return cudaErrorInvalidValue;
-    const int smem = ks2_smem_bytes(NG * SG, key.ks_stride);
+    const int smem = ks2_smem_bytes(NG * SG, key.ks_stride, ks2_stages(NG));
     if (smem > 227 * 1024) return cudaErrorInvalidValue;
     if (!(dev < 16 && done[dev])) {
         cudaError_t e = cudaFuncSetAttribute(k_keyswitch_tma<TG, NG, SG, NC, MODE, STRIDE4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
